@@ -1,0 +1,216 @@
+/* p1gpu.h — C-ABI of libp1gpu.so: B200 (sm_100a) kernels for linreg-mpc's phase-1
+ * secure aggregation.  This is the drop-in boundary: the reference's host code keeps
+ * its own entry points (run_trusted_initializer / run_party, src/phase1.h:14-29) and
+ * calls the functions below where src/phase1.c, src/linear.c and src/fixed.c do the
+ * arithmetic today.  Each entry cites the reference block it replaces (paths are
+ * under the reference tree).  No torch types, plain pointers and sizes only.
+ *
+ * Conventions (mirroring src/check_error.h:5-9 and src/phase1.c:644-655):
+ *   - every call returns 0 on success, 1 on failure; on failure a message is printed
+ *     to stderr and kept for p1_last_error(); outputs are left NULL/untouched.
+ *   - there is NO CPU fallback: without a CUDA device every call fails.
+ *   - ring width is chosen at context creation (the reference's compile-time
+ *     BIT_WIDTH_32_P1 / BIT_WIDTH_32_P2, src/fixed.h:4-30): (p1,p2) in
+ *     {(64,64),(32,32),(64,32)}.
+ *   - "ring word" = ufixed_p1_t: uint64_t when ring_bits_p1 == 64, else uint32_t.
+ *   - pointers named *_dev must be device pointers of the context's GPU; pointers
+ *     documented "host or device" are classified with cudaPointerGetAttributes.
+ *   - share accumulators are always uint64_t (a Z_2^32 share is the low half), so a
+ *     wrapping 64-bit sum all-reduce (NCCL ncclUint64/ncclSum) combines row shards
+ *     exactly for both rings.
+ *   - a context owns one CUDA stream; calls are asynchronous on it unless they return
+ *     host data.  Calls on one context are serialised by an internal mutex, so the
+ *     per-peer pthreads of OT mode (src/phase1.c:503-513) may share a context.
+ */
+#ifndef P1GPU_H
+#define P1GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct p1_ctx p1_ctx;
+typedef struct p1_data p1_data;       /* encoded X (and y), resident in HBM, column-major */
+typedef struct p1_cot p1_cot;         /* one correlated-OT session with one peer */
+
+/* ------------------------------------------------------------------ context */
+
+int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_ctx **ctx);
+void p1_ctx_destroy(p1_ctx *ctx);
+const char *p1_last_error(void);
+int p1_ctx_sync(p1_ctx *ctx);
+/* make `waiter`'s stream wait for everything enqueued so far on `signaler`'s stream
+ * (a message hand-over between two parties that live on the same GPU) */
+int p1_ctx_wait(p1_ctx *waiter, p1_ctx *signaler);
+/* the context's cudaStream_t, for callers that time with CUDA events */
+void *p1_ctx_stream(p1_ctx *ctx);
+/* number of kernels this context has launched so far */
+uint64_t p1_ctx_launches(p1_ctx *ctx);
+
+int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
+int p1_dev_free(p1_ctx *ctx, void *dev);
+int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes);
+int p1_copy_h2d(p1_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
+int p1_copy_d2h(p1_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes); /* synchronises */
+
+/* ------------------------------------------------------------------ a2-a4: encode
+ * Replaces the arithmetic of read_matrix / read_vector (src/linear.c:46-51,83-87):
+ *     val /= normalizer;  word = (fixed_p1_t) double_to_fixed(val, precision)
+ * with double_to_fixed = (fixed_t)(val * (1ll << precision)) (src/fixed.c:3-5), C
+ * truncation with x86 cvttsd2si semantics (out of range / NaN -> INT_MIN of the
+ * PHASE-2 width), then sign extension into the phase-1 ring.  Text parsing stays on
+ * the host.  normalizer = sqrt(pow(2,precision) * n_total) (src/phase1.c:473).
+ *   X : n x d row-major doubles (value[i*d+j], src/linear.c:51), host or device.
+ *   y : n doubles or NULL (only the last provider needs the target).
+ * The result lives on the GPU column-major (one contiguous n-vector per feature; the
+ * target is column d), which is what every consumer below streams.  Per-column
+ * statistics (max |word|, exact sum of squares) are gathered in the same pass. */
+int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n, size_t d,
+              double normalizer, int precision, p1_data **out);
+/* same, from ring words that are already encoded (row-major n x d, and n) */
+int p1_data_from_words(p1_ctx *ctx, const void *X_words, const void *y_words, size_t n, size_t d,
+                       p1_data **out);
+void p1_data_free(p1_data *data);
+/* encoded words back in the reference's layout (matrix_t.value row-major, vector_t.value) */
+int p1_data_download(p1_ctx *ctx, const p1_data *data, void *X_words, void *y_words);
+size_t p1_data_rows(const p1_data *data);
+size_t p1_data_cols(const p1_data *data);
+/* device pointer and leading dimension (in words) of the column-major store */
+const void *p1_data_colmajor_dev(const p1_data *data, size_t *ld_words);
+
+/* ------------------------------------------------------------------ share accumulator
+ * layout of the uint64_t accumulator every call below adds into (length p1_acc_len(d)):
+ *     [0, nA)            share_A, packed lower triangle, idx(i,j) = i(i+1)/2 + j (src/linear.c:11-16)
+ *     [nA, nA+d)         share_b
+ *     [nA+d, nA+2d)      diagonal: low  32-bit halves summed: sum_k (word_k^2 & 0xffffffff)
+ *     [nA+2d, nA+3d)     diagonal: high halves summed:        sum_k (word_k^2 >> 32)
+ *     [nA+3d, nA+4d)     diagonal: number of rows with |word| >= 2^26
+ * All entries are sums over rows, so row shards combine by a wrapping u64 all-reduce. */
+size_t p1_acc_len(size_t d);
+
+/* ------------------------------------------------------------------ a7/a8: local block
+ * Replaces the "own both" branch and the diagonal branch of the pair loop
+ * (src/phase1.c:562-571; OT-mode copy :359-383) for the provider owning columns
+ * [col_lo, col_hi): for every pair col_lo <= j < i < col_hi
+ *     acc[idx(i,j)] += sum_k X[k][i] * X[k][j]            (inner_product_local, :14-20)
+ * and, if owns_target, acc[nA + j] += sum_k y[k] * X[k][j] for every owned j (:540-543),
+ * plus the diagonal statistics of the owned columns (see p1_finalize).
+ * algo: 0 = choose by size, 1 = 64-bit IMAD CUDA-core kernel, 2 = tcgen05 kind::i8
+ * signed-limb GEMM (TMA -> smem -> tensor core -> TMEM). */
+#define P1_GRAM_AUTO 0
+#define P1_GRAM_IMAD 1
+#define P1_GRAM_TCGEN05 2
+int p1_local_block(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target,
+                   uint64_t *acc_dev, int algo);
+
+/* Sequential double-precision diagonal, the literal loop of src/phase1.c:563-566:
+ *     for k: xy += pow(fixed_to_double_p1(word_k, precision), 2) * pow(2, precision)
+ * continued from xy_inout[c] over this shard's rows for columns col_lo..col_hi-1
+ * (host array of col_hi-col_lo doubles).  Only needed when p1_finalize reports that
+ * the exact integer shortcut does not apply; row shards chain it in rank order. */
+int p1_diag_sequential(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int precision,
+                       double *xy_inout);
+
+/* ------------------------------------------------------------------ a9: trusted initializer
+ * Replaces the body of the TI loop (src/phase1.c:270-278) for cross pairs
+ * q0 .. q0+count-1 (q = running index of the pair in the loop order of :257-267).
+ * Mask stream: AES-128-CTR keystream S under `key`, zero IV, 128-bit big-endian block
+ * counter; the TI's randomizeBuffer calls read S consecutively, so pair q owns the words
+ *     x = S[W0 .. W0+n), y = S[W0+n .. W0+2n), r = S[W0+2n],  W0 = q*(2*n_total+1)
+ * (words = keystream bytes in host little-endian order).  Only rows
+ * [row0, row0+n_rows) are produced (row sharding; CTR is random access).
+ *   x_dev, y_dev : count vectors of n_rows words, ld_words apart; either may be NULL
+ *                  (a provider expanding only its own mask from a seed, or the TI
+ *                  computing only the values).
+ *   xy_dev       : count u64, WRITTEN with sum over the shard's rows of x*y; NULL to skip
+ *                  (needs both masks generated, stored or not).
+ *   r_dev        : count u64, written with r (identical on every shard); NULL to skip.
+ * The messages of :277-278 are then {vector = y, value = xy - r} and {vector = x, value = r}. */
+int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count,
+                   size_t n_total, size_t row0, size_t n_rows,
+                   void *x_dev, void *y_dev, size_t ld_words,
+                   uint64_t *xy_dev, uint64_t *r_dev);
+/* value_a[p] = xy[p] - r[p], value_b[p] = r[p] (src/phase1.c:277-278), after xy was all-reduced */
+int p1_ti_values(p1_ctx *ctx, const uint64_t *xy_dev, const uint64_t *r_dev, size_t count,
+                 uint64_t *value_a_dev, uint64_t *value_b_dev);
+
+/* ------------------------------------------------------------------ a10: inner_product_ti
+ * Batched party side of the masking protocol (src/phase1.c:173-224).  For pair p of
+ * the batch: cols[p] = this party's row of the pair (column index into `data`; d means
+ * the target vector), slots[p] = accumulator index (idx(i,j), or nA + j when i == d,
+ * src/phase1.c:581-585).  cols/slots: host or device arrays.
+ *   party b, step 1 (:202-205)  out[p][k]  = col[k] + T[p][k]                 (T = x)
+ *   party a         (:187-195)  out[p][k]  = col[k] - T[p][k]                 (T = y)
+ *                               acc[slot] += sum_k in[p][k] * T[p][k]
+ *   party b, step 2 (:221)      acc[slot] += sum_k in[p][k] * col[k]
+ *   both            (:196,222)  acc[slot] -= value[p]      (once, not per row shard)
+ * Vectors are n_rows(data) words long, ld_* words apart. */
+int p1_party_b_mask(p1_ctx *ctx, const p1_data *data, const int32_t *cols, size_t count,
+                    const void *T_dev, size_t ld_T, void *out_dev, size_t ld_out);
+int p1_party_a_step(p1_ctx *ctx, const p1_data *data, const int32_t *cols, const int64_t *slots, size_t count,
+                    const void *T_dev, size_t ld_T, const void *in_dev, size_t ld_in,
+                    void *out_dev, size_t ld_out, uint64_t *acc_dev);
+int p1_party_b_share(p1_ctx *ctx, const p1_data *data, const int32_t *cols, const int64_t *slots, size_t count,
+                     const void *in_dev, size_t ld_in, uint64_t *acc_dev);
+int p1_acc_sub_values(p1_ctx *ctx, uint64_t *acc_dev, const int64_t *slots, const uint64_t *value_dev, size_t count);
+
+/* ------------------------------------------------------------------ a12/a13: --use_ot
+ * Correlated-OT extension behind inner_product_ot_sender / inner_product_ot_recver
+ * (src/phase1.c:53-96).  The external Obliv-C primitive is replaced by the semi-honest
+ * IKNP-style construction defined in oracle/cot_ext.h (kappa = 128, AES-128-CTR column
+ * PRG, 128x128 bit transposes, fixed-key AES row hash); the base-OT outputs enter as
+ * seeds.  One inner product of n_rows words = n_rows * W OTs, OT index ni = k*W + bit
+ * (:45-46).  Wire messages stay on the device:
+ *   receiver -> sender : U, 2048 bytes per 128 OTs
+ *   sender -> receiver : C, one ring word per OT
+ * sender   (:43-51,66-68): opt0 = H(q), opt1 = (1<<bit)*x[k] + opt0, C = opt1 ^ H(q^Delta),
+ *                          acc[slot] += -sum opt0
+ * receiver (:78-83,90-92): choice = bit `bit` of a[k], dest = H(t) ^ (choice ? C : 0),
+ *                          acc[slot] += +sum dest */
+int p1_cot_sender_new(p1_ctx *ctx, const uint8_t delta[16], const uint8_t seeds[128][16], p1_cot **s);
+int p1_cot_receiver_new(p1_ctx *ctx, const uint8_t seeds0[128][16], const uint8_t seeds1[128][16], p1_cot **r);
+void p1_cot_free(p1_cot *session);
+/* wire sizes for an inner product over n_rows rows of this ring (row shard: row0 and
+ * n_rows must be multiples of 128/W words unless the shard is the last one) */
+size_t p1_cot_u_bytes(const p1_ctx *ctx, size_t n_rows);
+size_t p1_cot_c_bytes(const p1_ctx *ctx, size_t n_rows);
+/* receiver, first half: expands both column PRGs for the OTs of rows [row0, row0+n_rows)
+ * of an n_total-row inner product, writes U, keeps the hashed pads for _finish, and
+ * advances the session cursor by the whole inner product (n_total rows). */
+int p1_cot_receiver_extend(p1_ctx *ctx, p1_cot *r, const p1_data *data, int32_t col,
+                           size_t n_total, size_t row0, void *u_dev);
+/* sender: consumes U, writes C, adds -sum(opt0) into acc_dev[slot], advances the cursor */
+int p1_cot_sender_step(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col,
+                       size_t n_total, size_t row0, const void *u_dev,
+                       void *c_dev, uint64_t *acc_dev, int64_t slot);
+/* receiver, second half: adds +sum(dest) into acc_dev[slot] */
+int p1_cot_receiver_finish(p1_ctx *ctx, p1_cot *r, const void *c_dev, uint64_t *acc_dev, int64_t slot);
+
+/* ------------------------------------------------------------------ a14: finalize
+ * Tail of run_party (src/phase1.c:605-641).  `acc` (host or device, p1_acc_len(d)
+ * words, already summed over row shards) becomes the caller-owned calloc'ed arrays
+ * *res_A (d(d+1)/2 ufixed_t) and *res_b (d ufixed_t), which the caller free()s
+ * (src/cmd/linreg.c:203-204).  ufixed_t is uint64_t or uint32_t per ring_bits_p2.
+ *   - off-diagonal and share_b words: the ring word, and for (p1,p2) = (64,32) the
+ *     arithmetic shift (ufixed_t)(((fixed_p1_t) share) >> (precision - precision_p2)).
+ *   - diagonal words of owned columns [col_lo, col_hi) (src/phase1.c:562-567):
+ *     share = double_to_fixed_p1(xy / normalizer2, precision), where xy is the
+ *     sequential double sum.  When no row of the column has |word| >= 2^26 and the
+ *     exact integer S = sum word^2 (from the accumulator) is <= 2^53, every partial
+ *     sum of the reference's loop is exactly representable, so xy = S * 2^-precision
+ *     exactly, in any summation order.  Otherwise the column's xy must be supplied in
+ *     diag_xy[c - col_lo] (from p1_diag_sequential); if diag_xy is NULL or the entry is
+ *     NaN the call fails and lists the column in need_sequential (if not NULL, an
+ *     array of col_hi - col_lo ints set to 0/1). */
+int p1_finalize(p1_ctx *ctx, const uint64_t *acc, size_t d, size_t col_lo, size_t col_hi,
+                int precision, int precision_p2, double normalizer2,
+                const double *diag_xy, int *need_sequential,
+                void **res_A, void **res_b);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* P1GPU_H */

@@ -1,0 +1,313 @@
+// Correlated-OT extension for the --use_ot aggregation (src/phase1.c:43-96): the
+// construction of oracle/cot_ext.h on the GPU.  Tile = 128 consecutive OTs.
+//   per tile and column i (thread i of a 128-thread group): one AES-CTR block per seed
+//   (per-thread key schedules in shared memory), U = t ^ G(k1) ^ choice (receiver) or
+//   q = G(k) ^ Delta_i*U (sender); 128x128 bit transpose with warp ballots; per OT row
+//   (thread j): fixed-key AES hash, correlation (1<<bit)*x + opt0, wire word C.
+#include "p1_common.cuh"
+#include "aes_dev.cuh"
+#include <string.h>
+
+static const uint8_t COT_HASH_KEY[16] = { // "linreg-mpc-cot-H", as in oracle/cot_ext.c
+	0x6c, 0x69, 0x6e, 0x72, 0x65, 0x67, 0x2d, 0x6d, 0x70, 0x63, 0x2d, 0x63, 0x6f, 0x74, 0x2d, 0x48};
+
+struct p1_cot {
+	int device, bits;
+	int role;            // 0 receiver, 1 sender
+	uint32_t *keys_dev;  // [nk][44][128] round-key words, nk = 2 (receiver: k^0, k^1) or 1 (sender)
+	uint32_t delta[4];
+	uint64_t pos, ot_base;
+	// receiver state between _extend and _finish
+	void *pads;
+	size_t pads_bytes;
+	const void *col_ptr;
+	size_t n_rows;
+};
+
+#define COT_GROUPS 4
+#define COT_THREADS (128 * COT_GROUPS)
+
+struct CotParams {
+	AesKey hash;
+	const uint32_t *T0;
+	const uint32_t *keys;   // device key schedules
+	uint32_t delta[4];
+	uint64_t ctr0;          // PRG block of local tile 0
+	uint64_t J0;            // OT counter of local OT 0
+	uint64_t tiles;         // local tiles
+	uint64_t n_rows;
+	const void *col;        // this party's column (choice bits / correlator input)
+	void *u;                // wire U
+	void *c;                // wire C (sender)
+	void *pads;             // receiver stash
+	uint64_t *acc;          // sender: acc[slot] -= sum opt0
+};
+
+__device__ __forceinline__ void group_sync(int g) {
+	asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(128) : "memory");
+}
+
+// ROLE 0: receiver extend, ROLE 1: sender step
+template <typename W, int ROLE>
+__global__ void __launch_bounds__(COT_THREADS) k_cot_tiles(const CotParams P) {
+	extern __shared__ __align__(16) uint32_t smem[];
+	constexpr int NK = ROLE == 0 ? 2 : 1;
+	constexpr int WB = sizeof(W) * 8;
+	uint32_t *sT = smem;                       // 256 x 32 replicated T0
+	uint32_t *sK = sT + 256 * 32;              // NK x 44 x 128
+	uint32_t *sR = sK + NK * 44 * 128;         // COT_GROUPS x 128 x 5
+	aes_load_tables<32, 1>(sT, P.T0);
+	for(int i = threadIdx.x; i < NK * 44 * 128; i += blockDim.x) sK[i] = P.keys[i];
+	__syncthreads();
+	const int g = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5, lane = t & 31;
+	uint32_t *myR = sR + g * 128 * 5;
+	const bool dbit = ROLE == 1 && ((P.delta[t >> 5] >> (t & 31)) & 1);
+	uint64_t dot = 0;
+	for(uint64_t tile = (uint64_t) blockIdx.x * COT_GROUPS + g; tile < P.tiles; tile += (uint64_t) gridDim.x * COT_GROUPS) {
+		// ---- column phase: thread t = column t of the kappa x m matrix
+		uint32_t a[4];
+		aes_ctr_block_k<32, 1>(AesSmemKey(sK, 128, t), sT, lane, P.ctr0 + tile, a);
+		uint4 *up = reinterpret_cast<uint4 *>((char *) P.u + tile * 2048) + t;
+		if(ROLE == 0) {
+			uint32_t b[4];
+			aes_ctr_block_k<32, 1>(AesSmemKey(sK + 44 * 128, 128, t), sT, lane, P.ctr0 + tile, b);
+			const uint4 ch = *(reinterpret_cast<const uint4 *>(P.col) + tile); // 128 choice bits = 16 bytes of the column
+			*up = make_uint4(a[0] ^ b[0] ^ ch.x, a[1] ^ b[1] ^ ch.y, a[2] ^ b[2] ^ ch.z, a[3] ^ b[3] ^ ch.w);
+		} else if(dbit) {
+			const uint4 uv = *up;
+			a[0] ^= uv.x; a[1] ^= uv.y; a[2] ^= uv.z; a[3] ^= uv.w;
+		}
+		// ---- 128x128 bit transpose: ballot over the 32 columns of this warp
+		uint32_t keep[4];
+#pragma unroll
+		for(int b = 0; b < 4; b++) {
+			uint32_t mine = 0;
+#pragma unroll
+			for(int bit = 0; bit < 32; bit++) {
+				uint32_t v = __ballot_sync(0xffffffffu, (a[b] >> bit) & 1);
+				if(lane == bit) mine = v;
+			}
+			keep[b] = mine;
+		}
+#pragma unroll
+		for(int b = 0; b < 4; b++) myR[(32 * b + lane) * 5 + wq] = keep[b];
+		group_sync(g);
+		// ---- row phase: thread t = OT t of the tile
+		uint32_t x0 = myR[t * 5 + 0], x1 = myR[t * 5 + 1], x2 = myR[t * 5 + 2], x3 = myR[t * 5 + 3];
+		group_sync(g);
+		const uint64_t J = P.J0 + tile * 128 + t;
+		x0 ^= (uint32_t) J;
+		x1 ^= (uint32_t) (J >> 32);
+		uint32_t h[4];
+		aes_encrypt<32, 1>(AesConstKey(P.hash), sT, lane, x0, x1, x2, x3, h);
+		W pad0 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ x1)) << 32) | (h[0] ^ x0)) : (W) (h[0] ^ x0);
+		if(ROLE == 0) {
+			reinterpret_cast<W *>(P.pads)[tile * 128 + t] = pad0;
+		} else {
+			uint32_t y0 = x0 ^ P.delta[0], y1 = x1 ^ P.delta[1], y2 = x2 ^ P.delta[2], y3 = x3 ^ P.delta[3];
+			aes_encrypt<32, 1>(AesConstKey(P.hash), sT, lane, y0, y1, y2, y3, h);
+			W pad1 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ y1)) << 32) | (h[0] ^ y0)) : (W) (h[0] ^ y0);
+			const uint64_t ni = tile * 128 + t, k = ni / WB;
+			const int bit = (int) (ni % WB);
+			if(k < P.n_rows) {
+				W xk = reinterpret_cast<const W *>(P.col)[k];
+				W opt1 = (W) (xk << bit) + pad0; // (1 << bit) * x + opt0, src/phase1.c:50
+				reinterpret_cast<W *>(P.c)[ni] = opt1 ^ pad1;
+				dot -= (uint64_t) pad0;             // share = -sum opt0, src/phase1.c:66-68
+			}
+		}
+	}
+	if(ROLE == 1) {
+		__shared__ uint64_t part[COT_THREADS / 32];
+		dot = p1_warp_sum(dot);
+		if((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = dot;
+		__syncthreads();
+		if(threadIdx.x < 32) {
+			uint64_t s = threadIdx.x < COT_THREADS / 32 ? part[threadIdx.x] : 0;
+			s = p1_warp_sum(s);
+			if(threadIdx.x == 0 && s) p1_red_add(P.acc, s);
+		}
+	}
+}
+
+// receiver second half: dest = pad ^ (choice ? C : 0); share = +sum dest (src/phase1.c:90-92)
+template <typename W>
+__global__ void __launch_bounds__(256) k_cot_finish(const W *__restrict__ pads, const W *__restrict__ c, const W *__restrict__ col,
+	uint64_t m, uint64_t *__restrict__ acc) {
+	constexpr int WB = sizeof(W) * 8;
+	uint64_t dot = 0;
+	for(uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; j < m; j += (uint64_t) gridDim.x * blockDim.x) {
+		W a = col[j / WB];
+		W v = pads[j];
+		if((a >> (j % WB)) & 1) v ^= c[j];
+		dot += (uint64_t) v;
+	}
+	__shared__ uint64_t part[8];
+	dot = p1_warp_sum(dot);
+	if((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = dot;
+	__syncthreads();
+	if(threadIdx.x < 32) {
+		uint64_t s = threadIdx.x < 8 ? part[threadIdx.x] : 0;
+		s = p1_warp_sum(s);
+		if(threadIdx.x == 0 && s) p1_red_add(acc, s);
+	}
+}
+
+// ------------------------------------------------------------------ host
+
+#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
+
+static int cot_new(p1_ctx *ctx, int role, const uint8_t (*seeds_a)[16], const uint8_t (*seeds_b)[16], const uint8_t *delta, p1_cot **out) {
+	P1_CHECK(out, "null output");
+	*out = NULL;
+	int nk = role == 0 ? 2 : 1;
+	uint32_t *h = (uint32_t *) malloc((size_t) nk * 44 * 128 * sizeof(uint32_t));
+	P1_CHECK(h, "out of memory");
+	for(int kk = 0; kk < nk; kk++) {
+		for(int t = 0; t < 128; t++) {
+			AesKey K;
+			aes_host_expand(kk == 0 ? seeds_a[t] : seeds_b[t], &K);
+			for(int i = 0; i < 44; i++) h[((size_t) kk * 44 + i) * 128 + t] = K.rk[i];
+		}
+	}
+	p1_cot *s = new p1_cot();
+	s->device = ctx->device;
+	s->bits = ctx->bits_p1;
+	s->role = role;
+	s->pos = s->ot_base = 0;
+	s->pads = NULL;
+	s->pads_bytes = 0;
+	s->col_ptr = NULL;
+	s->n_rows = 0;
+	memset(s->delta, 0, sizeof(s->delta));
+	if(delta) memcpy(s->delta, delta, 16); // little-endian words: bit i of Delta = bit (i%8) of byte i/8
+	cudaError_t e = cudaMalloc(&s->keys_dev, (size_t) nk * 44 * 128 * sizeof(uint32_t));
+	if(e == cudaSuccess) e = cudaMemcpy(s->keys_dev, h, (size_t) nk * 44 * 128 * sizeof(uint32_t), cudaMemcpyHostToDevice);
+	free(h);
+	if(e != cudaSuccess) {
+		delete s;
+		return p1_fail("p1_cot_new: %s", cudaGetErrorString(e));
+	}
+	*out = s;
+	return 0;
+}
+
+extern "C" int p1_cot_sender_new(p1_ctx *ctx, const uint8_t delta[16], const uint8_t seeds[128][16], p1_cot **s) {
+	P1_ENTER(ctx);
+	P1_CHECK(delta && seeds, "p1_cot_sender_new: arguments may not be null");
+	return cot_new(ctx, 1, seeds, NULL, delta, s);
+}
+
+extern "C" int p1_cot_receiver_new(p1_ctx *ctx, const uint8_t seeds0[128][16], const uint8_t seeds1[128][16], p1_cot **r) {
+	P1_ENTER(ctx);
+	P1_CHECK(seeds0 && seeds1, "p1_cot_receiver_new: arguments may not be null");
+	return cot_new(ctx, 0, seeds0, seeds1, NULL, r);
+}
+
+extern "C" void p1_cot_free(p1_cot *s) {
+	if(!s) return;
+	cudaSetDevice(s->device);
+	cudaDeviceSynchronize();
+	cudaFree(s->keys_dev);
+	if(s->pads) cudaFree(s->pads);
+	delete s;
+}
+
+static size_t cot_tiles(int bits, size_t n_rows) { return (n_rows * (size_t) bits + 127) / 128; }
+
+extern "C" size_t p1_cot_u_bytes(const p1_ctx *ctx, size_t n_rows) { return ctx ? 2048 * cot_tiles(ctx->bits_p1, n_rows) : 0; }
+extern "C" size_t p1_cot_c_bytes(const p1_ctx *ctx, size_t n_rows) { return ctx ? 128 * (size_t) (ctx->bits_p1 / 8) * cot_tiles(ctx->bits_p1, n_rows) : 0; }
+
+template <int ROLE>
+static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, size_t n_total, size_t row0,
+	void *u_dev, void *c_dev, uint64_t *acc_slot) {
+	P1_CHECK(s && data, "null session or data");
+	P1_CHECK(s->role == (ROLE == 0 ? 0 : 1), "session has the other role");
+	P1_CHECK(s->bits == ctx->bits_p1 && data->bits == ctx->bits_p1, "ring width mismatch");
+	P1_CHECK(col >= 0 && (size_t) col <= data->d && ((size_t) col < data->d || data->has_y), "invalid column %d", col);
+	size_t per_tile = 128 / (size_t) s->bits; // rows per tile
+	P1_CHECK(row0 % per_tile == 0 && row0 + data->n <= n_total, "row shard [%zu,%zu) must start on a multiple of %zu rows inside [0,%zu)",
+		row0, row0 + data->n, per_tile, n_total);
+	P1_CHECK(row0 + data->n == n_total || data->n % per_tile == 0, "only the last row shard may hold a partial OT tile");
+	CotParams P;
+	aes_host_expand(COT_HASH_KEY, &P.hash);
+	if(aes_device_T0(ctx, &P.T0)) return 1;
+	P.keys = s->keys_dev;
+	memcpy(P.delta, s->delta, 16);
+	size_t tile0 = row0 * (size_t) s->bits / 128;
+	P.ctr0 = s->pos + tile0;
+	P.J0 = s->ot_base + 128 * (uint64_t) tile0;
+	P.tiles = cot_tiles(s->bits, data->n);
+	P.n_rows = data->n;
+	P.col = (const char *) data->xt + (size_t) col * data->ld * (size_t) (s->bits / 8);
+	P.u = u_dev;
+	P.c = c_dev;
+	P.acc = acc_slot;
+	P.pads = NULL;
+	if(ROLE == 0) {
+		size_t need = P.tiles * 128 * (size_t) (s->bits / 8);
+		if(s->pads_bytes < need) {
+			if(s->pads) {
+				P1_CUDA(cudaStreamSynchronize(ctx->stream));
+				P1_CUDA(cudaFree(s->pads));
+				s->pads = NULL;
+				s->pads_bytes = 0;
+			}
+			P1_CUDA(cudaMalloc(&s->pads, need));
+			s->pads_bytes = need;
+		}
+		P.pads = s->pads;
+		s->col_ptr = P.col;
+		s->n_rows = data->n;
+	}
+	constexpr int NK = ROLE == 0 ? 2 : 1;
+	size_t smem = (256 * 32 + NK * 44 * 128 + COT_GROUPS * 128 * 5) * sizeof(uint32_t);
+	uint64_t grid = (P.tiles + COT_GROUPS - 1) / COT_GROUPS;
+	int per_sm = 0;
+	if(s->bits == 64) {
+		P1_CUDA(cudaFuncSetAttribute(k_cot_tiles<uint64_t, ROLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_cot_tiles<uint64_t, ROLE>, COT_THREADS, smem));
+	} else {
+		P1_CUDA(cudaFuncSetAttribute(k_cot_tiles<uint32_t, ROLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_cot_tiles<uint32_t, ROLE>, COT_THREADS, smem));
+	}
+	P1_CHECK(per_sm > 0, "k_cot_tiles does not fit on an SM");
+	uint64_t cap = (uint64_t) ctx->sm_count * per_sm;
+	if(grid > cap) grid = cap;
+	if(s->bits == 64) k_cot_tiles<uint64_t, ROLE><<<(unsigned) grid, COT_THREADS, smem, ctx->stream>>>(P);
+	else k_cot_tiles<uint32_t, ROLE><<<(unsigned) grid, COT_THREADS, smem, ctx->stream>>>(P);
+	P1_LAUNCHED(ctx);
+	// the cursor moves by the WHOLE inner product, so every row shard stays in step
+	size_t tiles_total = cot_tiles(s->bits, n_total);
+	s->pos += tiles_total;
+	s->ot_base += 128 * (uint64_t) tiles_total;
+	return 0;
+}
+
+extern "C" int p1_cot_receiver_extend(p1_ctx *ctx, p1_cot *r, const p1_data *data, int32_t col,
+	size_t n_total, size_t row0, void *u_dev) {
+	P1_ENTER(ctx);
+	P1_CHECK(u_dev, "p1_cot_receiver_extend: null U buffer");
+	return cot_launch<0>(ctx, r, data, col, n_total, row0, u_dev, NULL, NULL);
+}
+
+extern "C" int p1_cot_sender_step(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col,
+	size_t n_total, size_t row0, const void *u_dev, void *c_dev, uint64_t *acc_dev, int64_t slot) {
+	P1_ENTER(ctx);
+	P1_CHECK(u_dev && c_dev && acc_dev, "p1_cot_sender_step: arguments may not be null");
+	return cot_launch<1>(ctx, s, data, col, n_total, row0, (void *) u_dev, c_dev, acc_dev + slot);
+}
+
+extern "C" int p1_cot_receiver_finish(p1_ctx *ctx, p1_cot *r, const void *c_dev, uint64_t *acc_dev, int64_t slot) {
+	P1_ENTER(ctx);
+	P1_CHECK(r && c_dev && acc_dev, "p1_cot_receiver_finish: arguments may not be null");
+	P1_CHECK(r->role == 0 && r->col_ptr, "p1_cot_receiver_finish: no extend pending on this session");
+	uint64_t m = (uint64_t) r->n_rows * (uint64_t) r->bits;
+	unsigned grid = (unsigned) ((m + 256 * 8 - 1) / (256 * 8));
+	if(grid > (unsigned) ctx->sm_count * 8) grid = ctx->sm_count * 8;
+	if(r->bits == 64) k_cot_finish<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) r->pads, (const uint64_t *) c_dev, (const uint64_t *) r->col_ptr, m, acc_dev + slot);
+	else k_cot_finish<uint32_t><<<grid, 256, 0, ctx->stream>>>((const uint32_t *) r->pads, (const uint32_t *) c_dev, (const uint32_t *) r->col_ptr, m, acc_dev + slot);
+	P1_LAUNCHED(ctx);
+	r->col_ptr = NULL;
+	return 0;
+}

@@ -1,0 +1,209 @@
+// Encode + layout kernels (HBM-bound streaming).
+//   k_rows_to_cols : row-major doubles (or ring words) -> column-major ring words,
+//                    fixed-point encode fused (src/linear.c:46-51, src/fixed.c:3-5) and
+//                    per-column statistics gathered in the same pass.
+//   k_vec_encode   : same for the target vector (src/linear.c:83-87).
+//   k_cols_to_rows : column-major -> the reference's row-major layout (tests / download).
+#include "p1_common.cuh"
+
+// (fixed_t) cast with x86 cvttsd2si semantics: truncate toward zero, INT_MIN of the
+// target width when out of range or NaN ("integer indefinite").  CUDA's cvt.rzi
+// saturates and maps NaN to 0, so the range test is explicit.
+template <int BITS>
+__device__ __forceinline__ int64_t cast_x86(double v) {
+	if(BITS == 64) {
+		if(!(v >= -9223372036854775808.0 && v < 9223372036854775808.0)) return INT64_MIN;
+		return __double2ll_rz(v);
+	} else {
+		if(!(v > -2147483649.0 && v < 2147483648.0)) return (int64_t) INT32_MIN;
+		return (int64_t) __double2int_rz(v);
+	}
+}
+
+struct EncodeParams {
+	double normalizer;
+	double scale;   // (double)(1ll << precision)
+	int bits_p2;
+};
+
+template <typename W, typename SRC>
+__device__ __forceinline__ W load_word(SRC v, const EncodeParams &ep);
+
+template <> __device__ __forceinline__ uint64_t load_word<uint64_t, double>(double v, const EncodeParams &ep) {
+	double t = __dmul_rn(__ddiv_rn(v, ep.normalizer), ep.scale); // val /= normalizer; val * (1ll<<p)
+	return (uint64_t) (ep.bits_p2 == 64 ? cast_x86<64>(t) : cast_x86<32>(t)); // sign-extends the 32-bit fixed_t
+}
+template <> __device__ __forceinline__ uint32_t load_word<uint32_t, double>(double v, const EncodeParams &ep) {
+	double t = __dmul_rn(__ddiv_rn(v, ep.normalizer), ep.scale);
+	return (uint32_t) cast_x86<32>(t);
+}
+template <> __device__ __forceinline__ uint64_t load_word<uint64_t, uint64_t>(uint64_t v, const EncodeParams &) { return v; }
+template <> __device__ __forceinline__ uint32_t load_word<uint32_t, uint32_t>(uint32_t v, const EncodeParams &) { return v; }
+
+struct ColStats {
+	uint64_t lo, hi, viol, mx;
+	__device__ __forceinline__ void init() { lo = hi = viol = mx = 0; }
+	template <typename W> __device__ __forceinline__ void add(W word) {
+		typedef typename p1_word<W>::s S;
+		int64_t s = (int64_t) (S) word;
+		uint64_t a = s < 0 ? (uint64_t) 0 - (uint64_t) s : (uint64_t) s;
+		uint64_t sq = a * a;
+		lo += sq & 0xffffffffull;
+		hi += sq >> 32;
+		viol += (a >> P1_SQ_LIMIT_BITS) ? 1 : 0;
+		mx = a > mx ? a : mx;
+	}
+	__device__ __forceinline__ void warp_reduce() {
+		lo = p1_warp_sum(lo);
+		hi = p1_warp_sum(hi);
+		viol = p1_warp_sum(viol);
+#pragma unroll
+		for(int o = 16; o; o >>= 1) {
+			uint64_t t = __shfl_xor_sync(0xffffffffu, mx, o);
+			mx = t > mx ? t : mx;
+		}
+	}
+	__device__ __forceinline__ void flush(uint64_t *st) {
+		p1_red_add(st + 0, lo);
+		p1_red_add(st + 1, hi);
+		if(viol) p1_red_add(st + 2, viol);
+		atomicMax(reinterpret_cast<unsigned long long *>(st + 3), (unsigned long long) mx);
+	}
+};
+
+#define ENC_ROWS_PER_CTA 512
+
+// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8)
+template <typename W, typename SRC>
+__global__ void __launch_bounds__(256) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep) {
+	__shared__ W tile[32][33];
+	const int tx = threadIdx.x, ty = threadIdx.y;
+	const size_t c0 = (size_t) blockIdx.x * 32;
+	const size_t rbase = (size_t) blockIdx.y * ENC_ROWS_PER_CTA;
+	ColStats cs[4];
+#pragma unroll
+	for(int u = 0; u < 4; u++) cs[u].init();
+	for(int sub = 0; sub < ENC_ROWS_PER_CTA / 32; sub++) {
+		size_t r0 = rbase + (size_t) sub * 32;
+		if(r0 >= rows) break;
+#pragma unroll
+		for(int u = 0; u < 4; u++) {
+			int rr = ty + 8 * u;
+			size_t r = r0 + rr, c = c0 + tx;
+			W wv = 0;
+			if(r < rows && c < d) wv = load_word<W, SRC>(src[r * d + c], ep);
+			tile[rr][tx] = wv;
+		}
+		__syncthreads();
+#pragma unroll
+		for(int u = 0; u < 4; u++) {
+			int cc = ty + 8 * u;
+			size_t c = c0 + cc, r = r0 + tx;
+			if(c < d && r < rows) {
+				W wv = tile[tx][cc];
+				xt[c * ld + row_off + r] = wv;
+				cs[u].add<W>(wv);
+			}
+		}
+		__syncthreads();
+	}
+#pragma unroll
+	for(int u = 0; u < 4; u++) {
+		cs[u].warp_reduce();
+		size_t c = c0 + ty + 8 * u;
+		if(tx == 0 && c < d) cs[u].flush(stats + 4 * c);
+	}
+}
+
+template <typename W, typename SRC>
+__global__ void __launch_bounds__(256) k_vec_encode(const SRC *__restrict__ src, size_t n, W *__restrict__ col,
+	uint64_t *__restrict__ stats, EncodeParams ep) {
+	ColStats cs;
+	cs.init();
+	for(size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		W wv = load_word<W, SRC>(src[i], ep);
+		col[i] = wv;
+		cs.add<W>(wv);
+	}
+	cs.warp_reduce();
+	if((threadIdx.x & 31) == 0) cs.flush(stats);
+}
+
+// grid (ceil(d/32), ceil(n/32)), block (32,8): column-major -> row-major
+template <typename W>
+__global__ void __launch_bounds__(256) k_cols_to_rows(const W *__restrict__ xt, size_t ld, size_t n, size_t d, W *__restrict__ dst) {
+	__shared__ W tile[32][33];
+	const int tx = threadIdx.x, ty = threadIdx.y;
+	const size_t c0 = (size_t) blockIdx.x * 32, r0 = (size_t) blockIdx.y * 32;
+#pragma unroll
+	for(int u = 0; u < 4; u++) {
+		int cc = ty + 8 * u;
+		size_t c = c0 + cc, r = r0 + tx;
+		tile[cc][tx] = (c < d && r < n) ? xt[c * ld + r] : (W) 0;
+	}
+	__syncthreads();
+#pragma unroll
+	for(int u = 0; u < 4; u++) {
+		int rr = ty + 8 * u;
+		size_t r = r0 + rr, c = c0 + tx;
+		if(r < n && c < d) dst[r * d + c] = tile[tx][rr];
+	}
+}
+
+template <typename W, typename SRC>
+static int launch_rows_to_cols(p1_ctx *ctx, const SRC *src, size_t rows, size_t d, size_t row_off, p1_data *out, EncodeParams ep) {
+	dim3 grid((unsigned) ((d + 31) / 32), (unsigned) ((rows + ENC_ROWS_PER_CTA - 1) / ENC_ROWS_PER_CTA)), block(32, 8);
+	k_rows_to_cols<W, SRC><<<grid, block, 0, ctx->stream>>>(src, rows, d, row_off, (W *) out->xt, out->ld, out->stats, ep);
+	P1_LAUNCHED(ctx);
+	return 0;
+}
+
+template <typename W, typename SRC>
+static int launch_vec(p1_ctx *ctx, const SRC *src, p1_data *out, EncodeParams ep) {
+	unsigned blocks = (unsigned) ((out->n + 256 * 8 - 1) / (256 * 8));
+	if(blocks > (unsigned) ctx->sm_count * 8) blocks = ctx->sm_count * 8;
+	k_vec_encode<W, SRC><<<blocks, 256, 0, ctx->stream>>>(src, out->n, (W *) out->xt + out->d * out->ld, out->stats + 4 * out->d, ep);
+	P1_LAUNCHED(ctx);
+	return 0;
+}
+
+int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
+	const double *y_dev, double normalizer, int precision, p1_data *out) {
+	EncodeParams ep = {normalizer, (double) (1ll << precision), ctx->bits_p2};
+	if(X_dev) {
+		if(out->bits == 64) { if(launch_rows_to_cols<uint64_t, double>(ctx, X_dev, rows, d, row_off, out, ep)) return 1; }
+		else { if(launch_rows_to_cols<uint32_t, double>(ctx, X_dev, rows, d, row_off, out, ep)) return 1; }
+	}
+	if(y_dev) {
+		if(out->bits == 64) return launch_vec<uint64_t, double>(ctx, y_dev, out, ep);
+		return launch_vec<uint32_t, double>(ctx, y_dev, out, ep);
+	}
+	return 0;
+}
+
+int p1_launch_words_in(p1_ctx *ctx, const void *Xw, const void *yw, p1_data *out) {
+	EncodeParams ep = {1.0, 1.0, ctx->bits_p2};
+	if(out->bits == 64) {
+		if(launch_rows_to_cols<uint64_t, uint64_t>(ctx, (const uint64_t *) Xw, out->n, out->d, 0, out, ep)) return 1;
+		if(yw) return launch_vec<uint64_t, uint64_t>(ctx, (const uint64_t *) yw, out, ep);
+	} else {
+		if(launch_rows_to_cols<uint32_t, uint32_t>(ctx, (const uint32_t *) Xw, out->n, out->d, 0, out, ep)) return 1;
+		if(yw) return launch_vec<uint32_t, uint32_t>(ctx, (const uint32_t *) yw, out, ep);
+	}
+	return 0;
+}
+
+int p1_launch_words_out(p1_ctx *ctx, const p1_data *dt, void *Xw, void *yw) {
+	size_t w = (size_t) dt->bits / 8;
+	if(Xw) {
+		dim3 grid((unsigned) ((dt->d + 31) / 32), (unsigned) ((dt->n + 31) / 32)), block(32, 8);
+		if(dt->bits == 64) k_cols_to_rows<uint64_t><<<grid, block, 0, ctx->stream>>>((const uint64_t *) dt->xt, dt->ld, dt->n, dt->d, (uint64_t *) Xw);
+		else k_cols_to_rows<uint32_t><<<grid, block, 0, ctx->stream>>>((const uint32_t *) dt->xt, dt->ld, dt->n, dt->d, (uint32_t *) Xw);
+		P1_LAUNCHED(ctx);
+	}
+	if(yw) {
+		P1_CUDA(cudaMemcpyAsync(yw, (const char *) dt->xt + dt->d * dt->ld * w, dt->n * w, cudaMemcpyDeviceToDevice, ctx->stream));
+	}
+	return 0;
+}

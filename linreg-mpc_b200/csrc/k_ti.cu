@@ -1,0 +1,261 @@
+// Trusted-initializer mask generation (src/phase1.c:270-278): AES-128-CTR expansion of
+// the masks x, y of a batch of cross pairs, fused with <x,y> and the draw of r.
+// Persistent kernel (one CTA set sized to the SM count; the replicated T-table is built
+// once per CTA), work unit = 32 lanes x TI_U consecutive stream blocks of one pair.
+#include "p1_common.cuh"
+#include "aes_dev.cuh"
+#include <string.h>
+
+// ------------------------------------------------------------------ host AES helpers
+
+static uint8_t h_sbox[256];
+static uint32_t h_T0[256];
+static bool h_ready = false;
+static std::mutex h_mu;
+
+static uint8_t gmul(uint8_t a, uint8_t b) {
+	uint8_t p = 0;
+	for(int i = 0; i < 8; i++) {
+		if(b & 1) p ^= a;
+		uint8_t hi = a & 0x80;
+		a <<= 1;
+		if(hi) a ^= 0x1b;
+		b >>= 1;
+	}
+	return p;
+}
+
+static void host_init(void) {
+	std::lock_guard<std::mutex> l(h_mu);
+	if(h_ready) return;
+	for(int x = 0; x < 256; x++) {
+		uint8_t inv = 0;
+		if(x) {
+			uint8_t r = 1, b = (uint8_t) x;
+			for(int e = 254; e; e >>= 1) {
+				if(e & 1) r = gmul(r, b);
+				b = gmul(b, b);
+			}
+			inv = r;
+		}
+		uint8_t s = inv;
+		for(int i = 1; i <= 4; i++) s ^= (uint8_t) ((inv << i) | (inv >> (8 - i)));
+		h_sbox[x] = s ^ 0x63;
+	}
+	for(int x = 0; x < 256; x++) {
+		uint32_t s = h_sbox[x];
+		h_T0[x] = (uint32_t) gmul((uint8_t) s, 2) | (s << 8) | (s << 16) | ((uint32_t) gmul((uint8_t) s, 3) << 24);
+	}
+	h_ready = true;
+}
+
+void aes_host_expand(const uint8_t key[16], AesKey *out) {
+	host_init();
+	uint8_t rk[176];
+	memcpy(rk, key, 16);
+	uint8_t rcon = 1;
+	for(int r = 1; r <= 10; r++) {
+		const uint8_t *p = rk + 16 * (r - 1);
+		uint8_t *q = rk + 16 * r;
+		uint8_t t[4] = {(uint8_t) (h_sbox[p[13]] ^ rcon), h_sbox[p[14]], h_sbox[p[15]], h_sbox[p[12]]};
+		rcon = gmul(rcon, 2);
+		for(int i = 0; i < 4; i++) q[i] = p[i] ^ t[i];
+		for(int i = 4; i < 16; i++) q[i] = p[i] ^ q[i - 4];
+	}
+	for(int i = 0; i < 44; i++) {
+		out->rk[i] = (uint32_t) rk[4 * i] | ((uint32_t) rk[4 * i + 1] << 8) | ((uint32_t) rk[4 * i + 2] << 16) | ((uint32_t) rk[4 * i + 3] << 24);
+	}
+}
+
+const uint32_t *aes_host_T0(void) {
+	host_init();
+	return h_T0;
+}
+
+static uint32_t *d_T0[64] = {NULL};
+
+int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
+	const uint32_t *t = aes_host_T0();
+	std::lock_guard<std::mutex> l(h_mu);
+	P1_CHECK(ctx->device < 64, "device index too large");
+	if(!d_T0[ctx->device]) {
+		uint32_t *p = NULL;
+		P1_CUDA(cudaMalloc(&p, sizeof(h_T0)));
+		P1_CUDA(cudaMemcpy(p, t, sizeof(h_T0), cudaMemcpyHostToDevice));
+		d_T0[ctx->device] = p;
+	}
+	*dT0 = d_T0[ctx->device];
+	return 0;
+}
+
+// ------------------------------------------------------------------ kernel
+
+#define TI_U 4 // stream blocks per lane per work unit
+
+struct TiParams {
+	AesKey key;
+	uint64_t q0;
+	uint32_t count;
+	uint64_t n_total, row0, n_rows;
+	void *x, *y;       // may be NULL
+	uint64_t ld;       // words between pairs
+	uint64_t *xy, *r;  // may be NULL
+	uint32_t units_per_pair;
+	const uint32_t *T0;
+};
+
+template <typename W, int REPL, int NTAB, bool ALIGNED>
+__global__ void __launch_bounds__(512) k_ti_generate(const TiParams P) {
+	extern __shared__ __align__(16) uint32_t sT[];
+	constexpr int w = sizeof(W);
+	constexpr int EPB = 16 / w; // elements per AES block
+	aes_load_tables<REPL, NTAB>(sT, P.T0);
+	__syncthreads();
+	const uint32_t lane = threadIdx.x & 31, lane_off = lane & (REPL - 1);
+	const uint64_t warps_total = (uint64_t) gridDim.x * (blockDim.x >> 5);
+	const uint64_t gw = (uint64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const uint64_t units = (uint64_t) P.count * P.units_per_pair;
+	const bool need_x = P.x || P.xy, need_y = P.y || P.xy;
+	const uint64_t nbytes = P.n_rows * w;        // bytes of one mask on this shard
+	const uint64_t ydelta = P.n_total * w;       // stream distance x -> y
+	const uint32_t ysh = (uint32_t) (ydelta & 15);
+
+	for(uint64_t u = gw; u < units; u += warps_total) {
+		const uint32_t p = (uint32_t) (u / P.units_per_pair), uu = (uint32_t) (u % P.units_per_pair);
+		const uint64_t W0 = (P.q0 + p) * (2 * P.n_total + 1);
+		const uint64_t X0 = (W0 + P.row0) * w;       // stream byte of this shard's x[0]
+		const uint64_t b_first = X0 >> 4;
+		W *xo = P.x ? (W *) P.x + (uint64_t) p * P.ld : nullptr;
+		W *yo = P.y ? (W *) P.y + (uint64_t) p * P.ld : nullptr;
+		uint64_t dot = 0;
+#pragma unroll 1
+		for(int i = 0; i < TI_U; i++) {
+			const uint64_t B = b_first + (uint64_t) uu * (32 * TI_U) + i * 32 + lane;
+			const int64_t o = (int64_t) (B << 4) - (int64_t) X0; // byte offset of this block in the shard's mask
+			if(o >= (int64_t) nbytes) continue;                  // past the end (o > -16 always)
+			uint32_t xs[4] = {0, 0, 0, 0}, ys[4] = {0, 0, 0, 0};
+			if(need_x) aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, B, xs);
+			if(need_y) {
+				const uint64_t By = ((B << 4) + ydelta) >> 4;
+				if(ALIGNED) {
+					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By, ys);
+				} else {
+					// y bytes for these positions straddle two stream blocks
+					uint32_t ya[4], yb[4];
+					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By, ya);
+					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By + 1, yb);
+					const uint32_t ws = ysh >> 2; // whole 32-bit words (ysh is a multiple of w >= 4)
+#pragma unroll
+					for(int c = 0; c < 4; c++) {
+						uint32_t idx = c + ws;
+						uint32_t v = 0;
+#pragma unroll
+						for(int z = 0; z < 8; z++) if(idx == (uint32_t) z) v = z < 4 ? ya[z & 3] : yb[z & 3];
+						ys[c] = v;
+					}
+				}
+			}
+#pragma unroll
+			for(int e = 0; e < EPB; e++) {
+				const int64_t ob = o + e * w;
+				if(ob < 0 || ob + w > (int64_t) nbytes) continue;
+				W xv, yv;
+				if(w == 8) {
+					xv = (W) (((uint64_t) xs[2 * e + 1] << 32) | xs[2 * e]);
+					yv = (W) (((uint64_t) ys[2 * e + 1] << 32) | ys[2 * e]);
+				} else {
+					xv = (W) xs[e];
+					yv = (W) ys[e];
+				}
+				const uint64_t k = (uint64_t) ob / w;
+				if(xo) xo[k] = xv;
+				if(yo) yo[k] = yv;
+				dot += (uint64_t) xv * (uint64_t) yv;
+			}
+		}
+		if(P.xy) {
+			dot = p1_warp_sum(dot);
+			if(lane == 0 && dot) p1_red_add(P.xy + p, dot);
+		}
+		if(P.r && uu == 0) {
+			// r = S[W0 + 2 n_total] (src/phase1.c:273)
+			const uint64_t Rb = (W0 + 2 * P.n_total) * w;
+			uint32_t rs[4];
+			aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, Rb >> 4, rs);
+			const uint32_t wi = (uint32_t) (Rb & 15) >> 2;
+			uint32_t lo = 0, hi = 0;
+#pragma unroll
+			for(int z = 0; z < 4; z++) {
+				if(wi == (uint32_t) z) lo = rs[z];
+				if(w == 8 && wi + 1 == (uint32_t) z) hi = rs[z];
+			}
+			if(lane == 0) P.r[p] = ((uint64_t) hi << 32) | lo;
+		}
+	}
+}
+
+template <typename W, int REPL, int NTAB>
+static int launch_ti(p1_ctx *ctx, const TiParams &P, bool aligned) {
+	size_t smem = (size_t) NTAB * 256 * REPL * sizeof(uint32_t);
+	int blocks_per_sm = 0;
+	if(aligned) {
+		P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, REPL, NTAB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_ti_generate<W, REPL, NTAB, true>, 512, smem));
+	} else {
+		P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, REPL, NTAB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_ti_generate<W, REPL, NTAB, false>, 512, smem));
+	}
+	P1_CHECK(blocks_per_sm > 0, "k_ti_generate does not fit on an SM");
+	uint64_t units = (uint64_t) P.count * P.units_per_pair;
+	uint64_t grid = (uint64_t) ctx->sm_count * blocks_per_sm;
+	uint64_t need = (units + 15) / 16; // 16 warps per CTA
+	if(grid > need) grid = need;
+	if(aligned) k_ti_generate<W, REPL, NTAB, true><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
+	else k_ti_generate<W, REPL, NTAB, false><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
+	P1_LAUNCHED(ctx);
+	return 0;
+}
+
+static int g_variant = -1; // 0: T0 x32 + PRMT rotations, 1: four stored tables x32
+
+extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count,
+	size_t n_total, size_t row0, size_t n_rows, void *x_dev, void *y_dev, size_t ld_words,
+	uint64_t *xy_dev, uint64_t *r_dev) {
+	P1_CHECK(ctx, "null context");
+	std::lock_guard<std::mutex> lock_(ctx->mu);
+	P1_CUDA(cudaSetDevice(ctx->device));
+	if(!count) return 0;
+	P1_CHECK(key, "p1_ti_generate: null key");
+	P1_CHECK(n_rows > 0 && row0 + n_rows <= n_total, "p1_ti_generate: rows [%zu,%zu) outside [0,%zu)", row0, row0 + n_rows, n_total);
+	P1_CHECK((!x_dev && !y_dev) || ld_words >= n_rows, "p1_ti_generate: ld_words %zu < n_rows %zu", ld_words, n_rows);
+	P1_CHECK(count <= 0xffffffffu, "p1_ti_generate: batch too large");
+	if(g_variant < 0) {
+		const char *e = getenv("P1_AES_VARIANT");
+		g_variant = e ? atoi(e) : 0;
+	}
+	const int w = ctx->bits_p1 / 8;
+	TiParams P;
+	if(aes_device_T0(ctx, &P.T0)) return 1;
+	aes_host_expand(key, &P.key);
+	P.q0 = q0;
+	P.count = (uint32_t) count;
+	P.n_total = n_total;
+	P.row0 = row0;
+	P.n_rows = n_rows;
+	P.x = x_dev;
+	P.y = y_dev;
+	P.ld = ld_words;
+	P.xy = xy_dev;
+	P.r = r_dev;
+	// stream blocks that can overlap one shard mask: bytes + up to 15 of misalignment
+	uint64_t nblk = ((uint64_t) n_rows * w + 15 + 15) / 16;
+	P.units_per_pair = (uint32_t) ((nblk + 32 * TI_U - 1) / (32 * TI_U));
+	if(xy_dev) P1_CUDA(cudaMemsetAsync(xy_dev, 0, count * sizeof(uint64_t), ctx->stream));
+	bool aligned = ((uint64_t) n_total * w) % 16 == 0;
+	if(w == 8) {
+		if(g_variant == 1) return launch_ti<uint64_t, 32, 4>(ctx, P, aligned);
+		return launch_ti<uint64_t, 32, 1>(ctx, P, aligned);
+	}
+	if(g_variant == 1) return launch_ti<uint32_t, 32, 4>(ctx, P, aligned);
+	return launch_ti<uint32_t, 32, 1>(ctx, P, aligned);
+}

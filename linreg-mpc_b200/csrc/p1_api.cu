@@ -1,0 +1,442 @@
+// C-ABI entry points of libp1gpu.so (include/p1gpu.h): context, memory, encode
+// orchestration, local-block dispatch, finalize.  Kernels live in the k_*.cu files.
+#include "p1_common.cuh"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+static thread_local char g_err[512] = "";
+
+int p1_fail(const char *fmt, ...) {
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+	fprintf(stderr, "p1gpu: %s\n", g_err);
+	return 1;
+}
+
+extern "C" const char *p1_last_error(void) { return g_err; }
+
+bool p1_is_device_ptr(const void *p) {
+	cudaPointerAttributes a;
+	if(cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+static const size_t SMALL_SLOTS = 4;
+
+int p1_small_to_dev(p1_ctx *ctx, const void *src, size_t bytes, size_t slot, const void **dev) {
+	if(p1_is_device_ptr(src)) {
+		*dev = src;
+		return 0;
+	}
+	size_t per = ctx->pin_bytes / SMALL_SLOTS;
+	P1_CHECK(bytes <= per && slot < SMALL_SLOTS, "index array of %zu bytes exceeds the %zu-byte staging slot; upload it once and pass the device pointer", bytes, per);
+	// the pinned slot may still be in flight from an earlier call: wait for the stream
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	char *h = (char *) ctx->pin + slot * per, *d = (char *) ctx->scratch + slot * per;
+	memcpy(h, src, bytes);
+	P1_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+	*dev = d;
+	return 0;
+}
+
+extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_ctx **out) {
+	P1_CHECK(out, "p1_ctx_create: out may not be null");
+	*out = NULL;
+	P1_CHECK((ring_bits_p1 == 64 && (ring_bits_p2 == 64 || ring_bits_p2 == 32)) || (ring_bits_p1 == 32 && ring_bits_p2 == 32),
+		"unsupported ring widths (%d,%d): supported are (64,64), (32,32), (64,32)", ring_bits_p1, ring_bits_p2);
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	P1_CHECK(e == cudaSuccess && count > 0, "no CUDA device available (%s); libp1gpu has no CPU fallback", cudaGetErrorString(e));
+	P1_CHECK(device >= 0 && device < count, "device %d out of range (%d devices)", device, count);
+	P1_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	P1_CUDA(cudaGetDeviceProperties(&prop, device));
+	P1_CHECK(prop.major == 10, "device %d is sm_%d%d; libp1gpu is built for sm_100a only", device, prop.major, prop.minor);
+	p1_ctx *ctx = new p1_ctx();
+	ctx->device = device;
+	ctx->bits_p1 = ring_bits_p1;
+	ctx->bits_p2 = ring_bits_p2;
+	ctx->sm_count = prop.multiProcessorCount;
+	ctx->launches = 0;
+	ctx->pin_bytes = ctx->scratch_bytes = 4u << 20;
+	ctx->stage[0] = ctx->stage[1] = NULL;
+	ctx->stage_bytes = 0;
+	ctx->limb_ws = NULL;
+	ctx->limb_ws_bytes = 0;
+	if(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+	   cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming) != cudaSuccess ||
+	   cudaMallocHost(&ctx->pin, ctx->pin_bytes) != cudaSuccess ||
+	   cudaMalloc(&ctx->scratch, ctx->scratch_bytes) != cudaSuccess) {
+		delete ctx;
+		return p1_fail("p1_ctx_create: %s", cudaGetErrorString(cudaGetLastError()));
+	}
+	*out = ctx;
+	return 0;
+}
+
+extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
+	if(!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	for(int i = 0; i < 2; i++) {
+		if(ctx->stage[i]) {
+			cudaFree(ctx->stage[i]);
+			cudaEventDestroy(ctx->stage_ev[i]);
+		}
+	}
+	if(ctx->limb_ws) cudaFree(ctx->limb_ws);
+	cudaFree(ctx->scratch);
+	cudaFreeHost(ctx->pin);
+	cudaEventDestroy(ctx->ev);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
+
+extern "C" int p1_ctx_sync(p1_ctx *ctx) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+extern "C" int p1_ctx_wait(p1_ctx *waiter, p1_ctx *signaler) {
+	P1_CHECK(waiter && signaler, "null context");
+	if(waiter == signaler) return 0;
+	{
+		std::lock_guard<std::mutex> l(signaler->mu);
+		P1_CUDA(cudaSetDevice(signaler->device));
+		P1_CUDA(cudaEventRecord(signaler->ev, signaler->stream));
+	}
+	std::lock_guard<std::mutex> l(waiter->mu);
+	P1_CUDA(cudaSetDevice(waiter->device));
+	P1_CUDA(cudaStreamWaitEvent(waiter->stream, signaler->ev, 0));
+	return 0;
+}
+
+extern "C" void *p1_ctx_stream(p1_ctx *ctx) { return ctx ? (void *) ctx->stream : NULL; }
+extern "C" uint64_t p1_ctx_launches(p1_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev) {
+	P1_ENTER(ctx);
+	P1_CHECK(dev, "null output");
+	*dev = NULL;
+	P1_CUDA(cudaMalloc(dev, bytes ? bytes : 1));
+	return 0;
+}
+extern "C" int p1_dev_free(p1_ctx *ctx, void *dev) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	P1_CUDA(cudaFree(dev));
+	return 0;
+}
+extern "C" int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaMemsetAsync(dev, 0, bytes, ctx->stream));
+	return 0;
+}
+extern "C" int p1_copy_h2d(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+	return 0;
+}
+extern "C" int p1_copy_d2h(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+// ------------------------------------------------------------------ data
+
+static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out) {
+	p1_data *dt = new p1_data();
+	dt->device = ctx->device;
+	dt->bits = ctx->bits_p1;
+	dt->n = n;
+	dt->d = d;
+	dt->has_y = has_y;
+	dt->ld = p1_round_up(n ? n : 1, 256);
+	dt->xt = NULL;
+	dt->stats = NULL;
+	size_t bytes = (d + 1) * dt->ld * (size_t) (dt->bits / 8);
+	if(cudaMalloc(&dt->xt, bytes) != cudaSuccess || cudaMalloc(&dt->stats, (d + 1) * 4 * sizeof(uint64_t)) != cudaSuccess) {
+		cudaError_t e = cudaGetLastError();
+		if(dt->xt) cudaFree(dt->xt);
+		delete dt;
+		return p1_fail("p1_encode: cannot allocate %zu bytes on device: %s", bytes, cudaGetErrorString(e));
+	}
+	// zero padding rows, the absent target column and the statistics
+	cudaMemsetAsync(dt->xt, 0, bytes, ctx->stream);
+	cudaMemsetAsync(dt->stats, 0, (d + 1) * 4 * sizeof(uint64_t), ctx->stream);
+	*out = dt;
+	return 0;
+}
+
+extern "C" void p1_data_free(p1_data *dt) {
+	if(!dt) return;
+	cudaSetDevice(dt->device);
+	cudaDeviceSynchronize();
+	cudaFree(dt->xt);
+	cudaFree(dt->stats);
+	delete dt;
+}
+
+extern "C" size_t p1_data_rows(const p1_data *dt) { return dt ? dt->n : 0; }
+extern "C" size_t p1_data_cols(const p1_data *dt) { return dt ? dt->d : 0; }
+extern "C" const void *p1_data_colmajor_dev(const p1_data *dt, size_t *ld) {
+	if(!dt) return NULL;
+	if(ld) *ld = dt->ld;
+	return dt->xt;
+}
+
+static int ensure_stage(p1_ctx *ctx, size_t bytes) {
+	if(ctx->stage_bytes >= bytes) return 0;
+	for(int i = 0; i < 2; i++) {
+		if(ctx->stage[i]) {
+			P1_CUDA(cudaStreamSynchronize(ctx->stream));
+			P1_CUDA(cudaFree(ctx->stage[i]));
+		} else {
+			P1_CUDA(cudaEventCreateWithFlags(&ctx->stage_ev[i], cudaEventDisableTiming));
+		}
+		ctx->stage[i] = NULL;
+		P1_CUDA(cudaMalloc(&ctx->stage[i], bytes));
+	}
+	ctx->stage_bytes = bytes;
+	return 0;
+}
+
+extern "C" int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n, size_t d,
+	double normalizer, int precision, p1_data **out) {
+	P1_ENTER(ctx);
+	P1_CHECK(out && X, "p1_encode: arguments may not be null");
+	*out = NULL;
+	P1_CHECK(n > 0 && d > 0, "p1_encode: empty matrix (%zu x %zu)", n, d);
+	P1_CHECK(precision >= 0 && precision < 63, "p1_encode: precision %d out of range", precision);
+	p1_data *dt = NULL;
+	if(data_alloc(ctx, n, d, y != NULL, &dt)) return 1;
+	int st = 0;
+	if(p1_is_device_ptr(X)) {
+		st = p1_launch_encode(ctx, X, n, d, 0, NULL, normalizer, precision, dt);
+	} else {
+		// host rows -> device staging (double-buffered) -> encode+transpose kernel
+		size_t row_bytes = d * sizeof(double);
+		size_t chunk_rows = (256u << 20) / row_bytes;
+		chunk_rows = chunk_rows / 256 * 256;
+		if(chunk_rows < 256) chunk_rows = 256;
+		if(chunk_rows > n) chunk_rows = n;
+		st = ensure_stage(ctx, chunk_rows * row_bytes);
+		int buf = 0;
+		for(size_t r0 = 0; r0 < n && !st; r0 += chunk_rows, buf ^= 1) {
+			size_t rows = n - r0 < chunk_rows ? n - r0 : chunk_rows;
+			// stage[buf] was last read by the encode launched two chunks ago on the same stream: ordered
+			if(cudaMemcpyAsync(ctx->stage[buf], X + r0 * d, rows * row_bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
+				st = p1_fail("p1_encode: H2D copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+				break;
+			}
+			st = p1_launch_encode(ctx, (const double *) ctx->stage[buf], rows, d, r0, NULL, normalizer, precision, dt);
+		}
+	}
+	if(!st && y) {
+		const double *y_dev = y;
+		if(!p1_is_device_ptr(y)) {
+			st = ensure_stage(ctx, n * sizeof(double));
+			if(!st && cudaMemcpyAsync(ctx->stage[0], y, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
+				st = p1_fail("p1_encode: H2D copy of y failed: %s", cudaGetErrorString(cudaGetLastError()));
+			}
+			y_dev = (const double *) ctx->stage[0];
+		}
+		if(!st) st = p1_launch_encode(ctx, NULL, n, d, 0, y_dev, normalizer, precision, dt);
+	}
+	if(st) {
+		p1_data_free(dt);
+		return 1;
+	}
+	*out = dt;
+	return 0;
+}
+
+extern "C" int p1_data_from_words(p1_ctx *ctx, const void *Xw, const void *yw, size_t n, size_t d, p1_data **out) {
+	P1_ENTER(ctx);
+	P1_CHECK(out && Xw, "p1_data_from_words: arguments may not be null");
+	*out = NULL;
+	P1_CHECK(n > 0 && d > 0, "p1_data_from_words: empty matrix");
+	p1_data *dt = NULL;
+	if(data_alloc(ctx, n, d, yw != NULL, &dt)) return 1;
+	size_t w = (size_t) ctx->bits_p1 / 8;
+	void *xd = NULL, *yd = NULL;
+	bool xfree = false, yfree = false;
+	int st = 0;
+	if(p1_is_device_ptr(Xw)) xd = (void *) Xw;
+	else {
+		if(cudaMalloc(&xd, n * d * w) != cudaSuccess) st = p1_fail("p1_data_from_words: out of device memory");
+		else {
+			xfree = true;
+			cudaMemcpyAsync(xd, Xw, n * d * w, cudaMemcpyHostToDevice, ctx->stream);
+		}
+	}
+	if(!st && yw) {
+		if(p1_is_device_ptr(yw)) yd = (void *) yw;
+		else {
+			if(cudaMalloc(&yd, n * w) != cudaSuccess) st = p1_fail("p1_data_from_words: out of device memory");
+			else {
+				yfree = true;
+				cudaMemcpyAsync(yd, yw, n * w, cudaMemcpyHostToDevice, ctx->stream);
+			}
+		}
+	}
+	if(!st) st = p1_launch_words_in(ctx, xd, yd, dt);
+	cudaStreamSynchronize(ctx->stream);
+	if(xfree) cudaFree(xd);
+	if(yfree) cudaFree(yd);
+	if(st) {
+		p1_data_free(dt);
+		return 1;
+	}
+	*out = dt;
+	return 0;
+}
+
+extern "C" int p1_data_download(p1_ctx *ctx, const p1_data *dt, void *Xw, void *yw) {
+	P1_ENTER(ctx);
+	P1_CHECK(dt, "null data");
+	size_t w = (size_t) dt->bits / 8;
+	void *xd = NULL, *yd = NULL;
+	if(Xw) P1_CUDA(cudaMalloc(&xd, dt->n * dt->d * w));
+	if(yw) P1_CUDA(cudaMalloc(&yd, dt->n * w));
+	int st = p1_launch_words_out(ctx, dt, xd, yd);
+	if(!st && Xw && cudaMemcpyAsync(Xw, xd, dt->n * dt->d * w, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) st = p1_fail("D2H failed");
+	if(!st && yw && cudaMemcpyAsync(yw, yd, dt->n * w, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) st = p1_fail("D2H failed");
+	cudaStreamSynchronize(ctx->stream);
+	cudaFree(xd);
+	cudaFree(yd);
+	return st;
+}
+
+// ------------------------------------------------------------------ local block
+
+extern "C" size_t p1_acc_len(size_t d) { return p1_nA(d) + 4 * d; }
+
+extern "C" int p1_local_block(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target,
+	uint64_t *acc_dev, int algo) {
+	P1_ENTER(ctx);
+	P1_CHECK(data && acc_dev, "p1_local_block: arguments may not be null");
+	P1_CHECK(col_lo <= col_hi && col_hi <= data->d, "p1_local_block: invalid column range [%zu,%zu) for d=%zu", col_lo, col_hi, data->d);
+	P1_CHECK(!owns_target || data->has_y, "p1_local_block: owns_target set but the data holds no target vector");
+	P1_CHECK(data->bits == ctx->bits_p1, "p1_local_block: data was encoded for a %d-bit ring", data->bits);
+	if(col_lo == col_hi) return 0;
+	if(p1_launch_diag_stats(ctx, data, col_lo, col_hi, acc_dev)) return 1;
+	size_t m = col_hi - col_lo + (owns_target ? 1 : 0);
+	if(m < 2) return 0;
+	if(algo == P1_GRAM_AUTO) {
+		// crossover measured on B200 (profiles/): the limb GEMM wins once the block fills a 128x128 tile
+		algo = (m >= 64 && data->n >= 4096) ? P1_GRAM_TCGEN05 : P1_GRAM_IMAD;
+	}
+	if(algo == P1_GRAM_TCGEN05) return p1_launch_gram_tc(ctx, data, col_lo, col_hi, owns_target, acc_dev);
+	P1_CHECK(algo == P1_GRAM_IMAD, "p1_local_block: unknown algo %d", algo);
+	return p1_launch_gram_imad(ctx, data, col_lo, col_hi, owns_target, acc_dev);
+}
+
+extern "C" int p1_diag_sequential(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int precision, double *xy_inout) {
+	P1_ENTER(ctx);
+	P1_CHECK(data && xy_inout, "p1_diag_sequential: arguments may not be null");
+	P1_CHECK(col_lo <= col_hi && col_hi <= data->d, "p1_diag_sequential: invalid column range");
+	size_t m = col_hi - col_lo;
+	if(!m) return 0;
+	double *xy_dev = NULL;
+	P1_CUDA(cudaMalloc(&xy_dev, m * sizeof(double)));
+	int st = 0;
+	if(cudaMemcpyAsync(xy_dev, xy_inout, m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) st = p1_fail("H2D failed");
+	if(!st) st = p1_launch_diag_seq(ctx, data, col_lo, col_hi, precision, xy_dev);
+	if(!st && cudaMemcpyAsync(xy_inout, xy_dev, m * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) st = p1_fail("D2H failed");
+	cudaStreamSynchronize(ctx->stream);
+	cudaFree(xy_dev);
+	return st;
+}
+
+// ------------------------------------------------------------------ finalize
+
+// (fixed_t)/(fixed_p1_t) cast of a double as x86-64 cvttsd2si does it (src/fixed.c:3-5,11-13)
+static int64_t cast_x86(double v, int bits) {
+	if(bits == 64) {
+		if(!(v >= -9223372036854775808.0 && v < 9223372036854775808.0)) return INT64_MIN;
+		return (int64_t) v;
+	}
+	if(!(v > -2147483649.0 && v < 2147483648.0)) return (int64_t) INT32_MIN;
+	return (int64_t) (int32_t) v;
+}
+
+extern "C" int p1_finalize(p1_ctx *ctx, const uint64_t *acc, size_t d, size_t col_lo, size_t col_hi,
+	int precision, int precision_p2, double normalizer2, const double *diag_xy, int *need_sequential,
+	void **res_A, void **res_b) {
+	P1_ENTER(ctx);
+	P1_CHECK(acc, "p1_finalize: null accumulator");
+	P1_CHECK(col_lo <= col_hi && col_hi <= d, "p1_finalize: invalid column range");
+	if(res_A) *res_A = NULL;
+	if(res_b) *res_b = NULL;
+	size_t nA = p1_nA(d), len = nA + 4 * d;
+	uint64_t *h = (uint64_t *) malloc(len * sizeof(uint64_t));
+	P1_CHECK(h, "out of memory");
+	if(p1_is_device_ptr(acc)) {
+		cudaError_t e = cudaMemcpyAsync(h, acc, len * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream);
+		if(e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+		if(e != cudaSuccess) {
+			free(h);
+			return p1_fail("p1_finalize: D2H failed: %s", cudaGetErrorString(e));
+		}
+	} else {
+		memcpy(h, acc, len * sizeof(uint64_t));
+	}
+	const int b1 = ctx->bits_p1, b2 = ctx->bits_p2;
+	// diagonal words (src/phase1.c:562-567)
+	int missing = 0;
+	for(size_t c = col_lo; c < col_hi; c++) {
+		uint64_t lo = h[nA + d + c], hi = h[nA + 2 * d + c], viol = h[nA + 3 * d + c];
+		unsigned __int128 S = ((unsigned __int128) hi << 32) + lo;
+		double xy;
+		bool exact = viol == 0 && S <= ((unsigned __int128) 1 << 53);
+		if(need_sequential) need_sequential[c - col_lo] = exact ? 0 : 1;
+		if(exact) {
+			xy = ldexp((double) (uint64_t) S, -precision);
+		} else if(diag_xy && !isnan(diag_xy[c - col_lo])) {
+			xy = diag_xy[c - col_lo];
+		} else {
+			missing++;
+			continue;
+		}
+		double scaled = (xy / normalizer2) * (double) (1ll << precision);
+		h[c * (c + 1) / 2 + c] = (uint64_t) cast_x86(scaled, b1);
+	}
+	if(missing) {
+		free(h);
+		return p1_fail("p1_finalize: %d diagonal column(s) need the sequential double sum (p1_diag_sequential)", missing);
+	}
+	size_t wout = (size_t) b2 / 8;
+	void *A = res_A ? calloc(nA ? nA : 1, b1 == 64 && b2 == 32 ? 8 : wout) : NULL; // reference over-allocates in the 64->32 case (src/phase1.c:611)
+	void *B = res_b ? calloc(d, b1 == 64 && b2 == 32 ? 8 : wout) : NULL;
+	if((res_A && !A) || (res_b && !B)) {
+		free(A);
+		free(B);
+		free(h);
+		return p1_fail("p1_finalize: out of memory");
+	}
+	for(size_t k = 0; k < nA + d; k++) {
+		void *dst = k < nA ? A : B;
+		size_t i = k < nA ? k : k - nA;
+		if(!dst) continue;
+		uint64_t v = h[k];
+		if(b1 == 64 && b2 == 64) ((uint64_t *) dst)[i] = v;
+		else if(b1 == 32) ((uint32_t *) dst)[i] = (uint32_t) v;
+		else ((uint32_t *) dst)[i] = (uint32_t) (((int64_t) v) >> (precision - precision_p2)); // src/phase1.c:617,633
+	}
+	free(h);
+	if(res_A) *res_A = A;
+	if(res_b) *res_b = B;
+	return 0;
+}

@@ -1,0 +1,79 @@
+// Internal declarations shared by the translation units of libp1gpu.so.
+// Public contract: include/p1gpu.h.  Target: sm_100a only.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <mutex>
+#include "../../include/p1gpu.h"
+
+#define P1_SQ_LIMIT_BITS 26   // |word| < 2^26  =>  v*v exact in binary64 (p1gpu.h, p1_finalize)
+
+struct p1_ctx {
+	int device;
+	int bits_p1, bits_p2;
+	int sm_count;
+	cudaStream_t stream;
+	cudaEvent_t ev;
+	std::mutex mu;
+	uint64_t launches;
+	// small pinned + device scratch for index arrays passed from the host
+	void *pin;      size_t pin_bytes;
+	void *scratch;  size_t scratch_bytes;
+	// staging for p1_encode from host memory (two buffers, events)
+	void *stage[2]; size_t stage_bytes; cudaEvent_t stage_ev[2];
+	// tcgen05 Gram workspace (limb planes), grown on demand
+	void *limb_ws;  size_t limb_ws_bytes;
+};
+
+struct p1_data {
+	int device, bits;
+	size_t n, d;        // rows, feature columns
+	bool has_y;         // column d holds the target
+	size_t ld;          // words between consecutive columns (n rounded up to 256)
+	void *xt;           // (d+1) x ld ring words, column-major; rows >= n are zero
+	uint64_t *stats;    // (d+1) x 4 : sq_lo, sq_hi, viol, maxabs
+};
+
+// error plumbing (check() of the reference: message to stderr, return 1)
+int p1_fail(const char *fmt, ...);
+#define P1_CHECK(cond, ...) do { if(!(cond)) return p1_fail(__VA_ARGS__); } while(0)
+#define P1_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) \
+	return p1_fail("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while(0)
+#define P1_LAUNCHED(ctx) do { (ctx)->launches++; cudaError_t e_ = cudaGetLastError(); if(e_ != cudaSuccess) \
+	return p1_fail("%s:%d: kernel launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); } while(0)
+
+static inline size_t p1_round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+static inline size_t p1_nA(size_t d) { return d * (d + 1) / 2; }
+
+// host or device pointer?
+bool p1_is_device_ptr(const void *p);
+// returns a device copy of a small host array (or the pointer itself if already on the device)
+int p1_small_to_dev(p1_ctx *ctx, const void *src, size_t bytes, size_t slot, const void **dev);
+
+// ---- launchers implemented in the kernel translation units ----
+int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
+	const double *y_dev, double normalizer, int precision, p1_data *out);
+int p1_launch_words_in(p1_ctx *ctx, const void *Xw_dev, const void *yw_dev, p1_data *out);
+int p1_launch_words_out(p1_ctx *ctx, const p1_data *data, void *Xw_dev, void *yw_dev);
+int p1_launch_gram_imad(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, uint64_t *acc_dev);
+int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, uint64_t *acc_dev);
+int p1_launch_diag_stats(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, uint64_t *acc_dev);
+int p1_launch_diag_seq(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int precision, double *xy_dev);
+
+// device helpers
+#ifdef __CUDACC__
+template <typename W> struct p1_word;
+template <> struct p1_word<uint64_t> { typedef int64_t s; static constexpr int bits = 64; };
+template <> struct p1_word<uint32_t> { typedef int32_t s; static constexpr int bits = 32; };
+
+__device__ __forceinline__ uint64_t p1_warp_sum(uint64_t v) {
+#pragma unroll
+	for(int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+__device__ __forceinline__ void p1_red_add(uint64_t *p, uint64_t v) {
+	atomicAdd(reinterpret_cast<unsigned long long *>(p), static_cast<unsigned long long>(v));
+}
+#endif

@@ -1,0 +1,379 @@
+"""GPU suite (-m gpu): every kernel of libp1gpu.so through the C-ABI against the oracle,
+bit-exact, plus whole phase-1 runs against the committed reference golden vectors."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+c_vp = ctypes.c_void_p
+WIDTHS = [(64, 64, 56, 0), (32, 32, 24, 0), (64, 32, 56, 24)]
+
+
+def mkctx(lib, b1=64, b2=64):
+    ctx = c_vp()
+    lib.check(lib.p1_ctx_create(0, b1, b2, ctypes.byref(ctx)))
+    return ctx
+
+
+def vp(a):
+    return a.ctypes.data_as(c_vp) if a is not None else None
+
+
+def encode(lib, ctx, X, y, normalizer, precision):
+    out = c_vp()
+    lib.check(lib.p1_encode(ctx, vp(X), vp(y), X.shape[0], X.shape[1], normalizer, precision, ctypes.byref(out)))
+    return out
+
+
+def from_words(lib, ctx, Xw, yw):
+    out = c_vp()
+    lib.check(lib.p1_data_from_words(ctx, vp(Xw), vp(yw), Xw.shape[0], Xw.shape[1], ctypes.byref(out)))
+    return out
+
+
+def download(lib, ctx, data, n, d, bits, with_y=True):
+    dt = po.word_dtype(bits)
+    Xw = np.empty((n, d), dt)
+    yw = np.empty(n, dt) if with_y else None
+    lib.check(lib.p1_data_download(ctx, data, vp(Xw), vp(yw)))
+    return Xw, yw
+
+
+def dev_array(lib, ctx, host):
+    p = c_vp()
+    lib.check(lib.p1_dev_alloc(ctx, max(host.nbytes, 8), ctypes.byref(p)))
+    lib.check(lib.p1_copy_h2d(ctx, p, vp(host), host.nbytes))
+    return p
+
+
+def dev_zeros(lib, ctx, nbytes):
+    p = c_vp()
+    lib.check(lib.p1_dev_alloc(ctx, max(nbytes, 8), ctypes.byref(p)))
+    lib.check(lib.p1_dev_zero(ctx, p, nbytes))
+    return p
+
+
+def to_host(lib, ctx, p, shape, dtype):
+    out = np.empty(shape, dtype)
+    lib.check(lib.p1_copy_d2h(ctx, vp(out), p, out.nbytes))
+    return out
+
+
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+def test_encode_parity(p1lib, oracle, b1, b2, prec, prec2):
+    rng = np.random.default_rng(1)
+    n, d = 777, 37  # ragged: not multiples of the 32x32 tiles
+    X = rng.standard_normal((n, d))
+    y = rng.standard_normal(n) * 3
+    # x86 cast edge cases (src/fixed.c:3-5 compiled by gcc): out of range, NaN, +-0, denormals
+    X[0, :8] = [1e30, -1e30, float("nan"), float("inf"), float("-inf"), 0.0, -0.0, 5e-324]
+    X[1, :4] = [2.0 ** 31, -2.0 ** 31, 2.0 ** 63, -2.0 ** 63]
+    y[:3] = [1e300, -1e300, float("nan")]
+    nz = oracle.normalizer(prec, n)
+    ctx = mkctx(p1lib, b1, b2)
+    data = encode(p1lib, ctx, X, y, nz, prec)
+    Xw, yw = download(p1lib, ctx, data, n, d, b1)
+    assert np.array_equal(Xw, oracle.encode(X, nz, prec, b1, b2))
+    assert np.array_equal(yw, oracle.encode(y, nz, prec, b1, b2))
+    # the same from device-resident doubles
+    import torch
+    Xd = torch.from_numpy(X).cuda()
+    out = c_vp()
+    p1lib.check(p1lib.p1_encode(ctx, c_vp(Xd.data_ptr()), None, n, d, nz, prec, ctypes.byref(out)))
+    Xw2, _ = download(p1lib, ctx, out, n, d, b1, with_y=False)
+    assert np.array_equal(Xw2, Xw)
+    p1lib.p1_data_free(out)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+def _check_local_block(p1lib, oracle, ctx, data, Xw, yw, lo, hi, owns_target, bits, algo):
+    n, d = Xw.shape
+    nA = d * (d + 1) // 2
+    L = int(p1lib.p1_acc_len(d))
+    acc = dev_zeros(p1lib, ctx, 8 * L)
+    p1lib.check(p1lib.p1_local_block(ctx, data, lo, hi, int(owns_target), acc, algo))
+    got = to_host(p1lib, ctx, acc, L, np.uint64)
+    mask = (1 << bits) - 1
+    want = np.zeros(nA + d, np.uint64)
+    for i in range(lo, hi):
+        for j in range(lo, i):
+            want[i * (i + 1) // 2 + j] = oracle.dot(Xw[:, i], Xw[:, j], bits)
+        if owns_target:
+            want[nA + i] = oracle.dot(yw, Xw[:, i], bits)
+    off = np.ones(nA + d, bool)
+    off[[i * (i + 1) // 2 + i for i in range(d)]] = False  # diagonal slots belong to the FP64 path
+    assert np.array_equal(got[:nA + d][off] & np.uint64(mask), want[off])
+    # diagonal statistics: exact sum of squares of the owned columns
+    for c in range(lo, hi):
+        col = Xw[:, c].astype(np.int64 if bits == 64 else np.int32).astype(object)
+        S = sum(int(v) * int(v) for v in col)
+        viol = sum(1 for v in col if abs(int(v)) >= 2 ** 26)
+        if viol == 0:
+            assert (int(got[nA + 2 * d + c]) << 32) + int(got[nA + d + c]) == S
+        assert int(got[nA + 3 * d + c]) == viol
+    p1lib.check(p1lib.p1_dev_free(ctx, acc))
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+def test_local_block_imad_parity(p1lib, oracle, b1, b2, prec, prec2):
+    n, d = 1500, 70  # two column tiles, ragged rows
+    X, y, _ = po.generate_lin_regression(n, d, seed=2)
+    nz = oracle.normalizer(prec, n)
+    ctx = mkctx(p1lib, b1, b2)
+    data = encode(p1lib, ctx, X, y, nz, prec)
+    Xw, yw = download(p1lib, ctx, data, n, d, b1)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, b1, 1)       # single provider: whole Gram + X^T y
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 20, 47, False, b1, 1)    # middle provider
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 47, 70, True, b1, 1)     # last provider
+    p1lib.p1_data_free(data)
+    # full-range ring words (the wide 64x64 IMAD path)
+    rng = np.random.default_rng(4)
+    dt = po.word_dtype(b1)
+    Xf = rng.integers(0, 2 ** 63, (600, 9), dtype=np.uint64).astype(dt) * dt(3)
+    yf = rng.integers(0, 2 ** 63, 600, dtype=np.uint64).astype(dt) * dt(5)
+    data = from_words(p1lib, ctx, Xf, yf)
+    _check_local_block(p1lib, oracle, ctx, data, Xf, yf, 0, 9, True, b1, 1)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
+def test_diagonal_exact_and_sequential(p1lib, oracle, bits):
+    b2 = bits
+    prec = 56 if bits == 64 else 24
+    ctx = mkctx(p1lib, bits, b2)
+    rng = np.random.default_rng(6)
+    n, d = 3000, 6
+    dt = po.word_dtype(bits)
+    sdt = np.int64 if bits == 64 else np.int32
+    lim = 2 ** 25 if bits == 64 else 2 ** 14
+    Xs = rng.integers(-lim, lim, (n, d)).astype(sdt)
+    if bits == 64:
+        Xs[:, 1] *= 2 ** 12      # |word| >= 2^26: the exact shortcut must be refused
+        Xs[:, 4] = rng.integers(2 ** 25, 2 ** 26, n)  # no single violation but sum of squares > 2^53
+    Xw = Xs.view(dt)
+    data = from_words(p1lib, ctx, Xw, None)
+    L = int(p1lib.p1_acc_len(d)); nA = d * (d + 1) // 2
+    acc = dev_zeros(p1lib, ctx, 8 * L)
+    p1lib.check(p1lib.p1_local_block(ctx, data, 0, d, 0, acc, 1))
+    need = (ctypes.c_int * d)()
+    A, B = c_vp(), c_vp()
+    st = p1lib.p1_finalize(ctx, acc, d, 0, d, prec, 0, float(d), None, need, ctypes.byref(A), ctypes.byref(B))
+    want_need = [0, 1, 0, 0, 1, 0] if bits == 64 else [0] * d
+    assert list(need) == want_need
+    xy = np.full(d, np.nan)
+    if any(want_need):
+        assert st == 1  # refuses to guess: the sequential sums are required
+        xy = np.zeros(d)
+        # chained in two row shards to exercise the continuation
+        h1 = from_words(p1lib, ctx, np.ascontiguousarray(Xw[:1234]), None)
+        h2 = from_words(p1lib, ctx, np.ascontiguousarray(Xw[1234:]), None)
+        p1lib.check(p1lib.p1_diag_sequential(ctx, h1, 0, d, prec, vp(xy)))
+        p1lib.check(p1lib.p1_diag_sequential(ctx, h2, 0, d, prec, vp(xy)))
+        p1lib.p1_data_free(h1); p1lib.p1_data_free(h2)
+        p1lib.check(p1lib.p1_finalize(ctx, acc, d, 0, d, prec, 0, float(d), vp(xy), None, ctypes.byref(A), ctypes.byref(B)))
+    else:
+        assert st == 0
+    resA = np.ctypeslib.as_array(ctypes.cast(A, ctypes.POINTER(ctypes.c_uint64 if bits == 64 else ctypes.c_uint32)), (nA,))
+    for c in range(d):
+        assert int(resA[c * (c + 1) // 2 + c]) == oracle.diag(Xw[:, c], prec, float(d), bits), c
+    # the sequential kernel equals the literal loop on every column, also where the shortcut applies
+    xy2 = np.zeros(d)
+    p1lib.check(p1lib.p1_diag_sequential(ctx, data, 0, d, prec, vp(xy2)))
+    for c in range(d):
+        acc_d = ctypes.c_double(0.0)
+        oracle.lib.p1o_diag_accumulate(vp(np.ascontiguousarray(Xw[:, c])), 1, n, prec, bits, ctypes.byref(acc_d))
+        assert xy2[c] == acc_d.value
+    p1lib.free(A); p1lib.free(B)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
+@pytest.mark.parametrize("n_total,row0,n_rows", [(1000, 0, 1000), (1001, 0, 1001), (1003, 0, 1003), (4096, 1024, 2048),
+                                                 (999, 333, 666), (130, 0, 130), (1, 0, 1)])
+def test_ti_generate_parity(p1lib, oracle, bits, n_total, row0, n_rows):
+    ctx = mkctx(p1lib, bits, bits)
+    dt = po.word_dtype(bits)
+    q0, count = 5, 4
+    ld = (n_rows + 255) // 256 * 256
+    x = dev_zeros(p1lib, ctx, count * ld * dt().nbytes)
+    y = dev_zeros(p1lib, ctx, count * ld * dt().nbytes)
+    xy = dev_zeros(p1lib, ctx, 8 * count)
+    r = dev_zeros(p1lib, ctx, 8 * count)
+    p1lib.check(p1lib.p1_ti_generate(ctx, po.TI_KEY, q0, count, n_total, row0, n_rows, x, y, ld, xy, r))
+    xh = to_host(p1lib, ctx, x, (count, ld), dt)
+    yh = to_host(p1lib, ctx, y, (count, ld), dt)
+    xyh = to_host(p1lib, ctx, xy, count, np.uint64)
+    rh = to_host(p1lib, ctx, r, count, np.uint64)
+    # values-only call (seeded mode on the TI side) gives the same dot products
+    xy2 = dev_zeros(p1lib, ctx, 8 * count)
+    p1lib.check(p1lib.p1_ti_generate(ctx, po.TI_KEY, q0, count, n_total, row0, n_rows, None, None, ld, xy2, None))
+    assert np.array_equal(to_host(p1lib, ctx, xy2, count, np.uint64), xyh)
+    mask = (1 << bits) - 1
+    for p in range(count):
+        xo, yo, va, vb = oracle.ti_pair(po.TI_KEY, q0 + p, n_total, bits)
+        assert np.array_equal(xh[p, :n_rows], xo[row0:row0 + n_rows]), p
+        assert np.array_equal(yh[p, :n_rows], yo[row0:row0 + n_rows]), p
+        assert not xh[p, n_rows:].any()  # padding untouched
+        assert int(rh[p]) == vb
+        assert int(xyh[p]) & mask == oracle.dot(xo[row0:row0 + n_rows], yo[row0:row0 + n_rows], bits)
+        if row0 == 0 and n_rows == n_total:
+            assert (int(xyh[p]) - int(rh[p])) & mask == va
+    for p_ in (x, y, xy, r, xy2):
+        p1lib.check(p1lib.p1_dev_free(ctx, p_))
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
+def test_party_kernels_parity(p1lib, oracle, bits):
+    ctx = mkctx(p1lib, bits, bits)
+    rng = np.random.default_rng(8)
+    dt = po.word_dtype(bits)
+    n, d, count = 2051, 7, 5  # ragged n exercises the scalar tail
+    Xw = rng.integers(0, 2 ** 63, (n, d), dtype=np.uint64).astype(dt)
+    yw = rng.integers(0, 2 ** 63, n, dtype=np.uint64).astype(dt)
+    data = from_words(p1lib, ctx, Xw, yw)
+    ld = (n + 255) // 256 * 256
+    T = rng.integers(0, 2 ** 63, (count, ld), dtype=np.uint64).astype(dt)
+    IN = rng.integers(0, 2 ** 63, (count, ld), dtype=np.uint64).astype(dt)
+    cols = np.array([0, 3, 7, 6, 3], np.int32)  # 7 = target vector
+    slots = np.array([2, 9, 4, 2, 11], np.int64)  # slot 2 hit twice: accumulation
+    colv = lambda c: yw if c == d else Xw[:, c]
+    Td, INd = dev_array(p1lib, ctx, T), dev_array(p1lib, ctx, IN)
+    out = dev_zeros(p1lib, ctx, T.nbytes)
+    acc = dev_zeros(p1lib, ctx, 8 * 16)
+    mask = (1 << bits) - 1
+    # b: out = col + T
+    p1lib.check(p1lib.p1_party_b_mask(ctx, data, vp(cols), count, Td, ld, out, ld))
+    oh = to_host(p1lib, ctx, out, (count, ld), dt)
+    for p in range(count):
+        assert np.array_equal(oh[p, :n], colv(cols[p]) + T[p, :n])
+    # a: out = col - T, acc += <in, T>
+    p1lib.check(p1lib.p1_party_a_step(ctx, data, vp(cols), vp(slots), count, Td, ld, INd, ld, out, ld, acc))
+    oh = to_host(p1lib, ctx, out, (count, ld), dt)
+    want = np.zeros(16, np.uint64)
+    for p in range(count):
+        assert np.array_equal(oh[p, :n], colv(cols[p]) - T[p, :n])
+        want[slots[p]] += np.uint64(oracle.dot(IN[p, :n], T[p, :n], bits))
+    got = to_host(p1lib, ctx, acc, 16, np.uint64)
+    assert np.array_equal(got & np.uint64(mask), want & np.uint64(mask))
+    # b: acc += <in, col>
+    p1lib.check(p1lib.p1_party_b_share(ctx, data, vp(cols), vp(slots), count, INd, ld, acc))
+    for p in range(count):
+        want[slots[p]] += np.uint64(oracle.dot(IN[p, :n], colv(cols[p]), bits))
+    got = to_host(p1lib, ctx, acc, 16, np.uint64)
+    assert np.array_equal(got & np.uint64(mask), want & np.uint64(mask))
+    # acc -= value
+    vals = rng.integers(0, 2 ** 63, count, dtype=np.uint64)
+    vd = dev_array(p1lib, ctx, vals)
+    p1lib.check(p1lib.p1_acc_sub_values(ctx, acc, vp(slots), vd, count))
+    for p in range(count):
+        want[slots[p]] -= vals[p]
+    got = to_host(p1lib, ctx, acc, 16, np.uint64)
+    assert np.array_equal(got & np.uint64(mask), want & np.uint64(mask))
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
+@pytest.mark.parametrize("n", [64, 37, 515])
+def test_cot_inner_product_parity(p1lib, oracle, bits, n):
+    """one OT-based inner product: both shares and both wire messages equal the oracle's"""
+    from linreg_mpc_b200 import phase1
+    ctx = mkctx(p1lib, bits, bits)
+    rng = np.random.default_rng(10)
+    dt = po.word_dtype(bits)
+    Xw = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64).astype(dt) * dt(3)
+    data = from_words(p1lib, ctx, Xw, None)
+    s0, s1, delta = phase1.derive_cot_session(po.OT_KEY, 2, 4)
+    chosen = np.ascontiguousarray(np.where(phase1._bits128(delta)[:, None], s1, s0))
+    snd, rcv = c_vp(), c_vp()
+    p1lib.check(p1lib.p1_cot_sender_new(ctx, delta.tobytes(), vp(chosen), ctypes.byref(snd)))
+    p1lib.check(p1lib.p1_cot_receiver_new(ctx, vp(s0), vp(s1), ctypes.byref(rcv)))
+    ub, cb = int(p1lib.p1_cot_u_bytes(ctx, n)), int(p1lib.p1_cot_c_bytes(ctx, n))
+    u = dev_zeros(p1lib, ctx, ub); c = dev_zeros(p1lib, ctx, cb)
+    acc = dev_zeros(p1lib, ctx, 16)
+    ss = oracle.lib.p1o_ot_session_new(po.OT_KEY, 2, 4)
+    want_s = want_r = 0
+    mask = (1 << bits) - 1
+    for rep in range(2):  # session cursor advances
+        p1lib.check(p1lib.p1_cot_receiver_extend(ctx, rcv, data, 1, n, 0, u))
+        p1lib.check(p1lib.p1_cot_sender_step(ctx, snd, data, 0, n, 0, u, c, acc, 0))
+        p1lib.check(p1lib.p1_cot_receiver_finish(ctx, rcv, c, acc, 1))
+        os_, or_, uo, co = oracle.ot_inner_product(ss, Xw[:, 0], Xw[:, 1], bits, want_wire=True)
+        assert np.array_equal(to_host(p1lib, ctx, u, ub, np.uint8), uo)
+        assert np.array_equal(to_host(p1lib, ctx, c, cb, np.uint8)[:co.size], co)
+        want_s = (want_s + os_) & mask; want_r = (want_r + or_) & mask
+        got = to_host(p1lib, ctx, acc, 2, np.uint64)
+        assert int(got[0]) & mask == want_s and int(got[1]) & mask == want_r
+    assert (want_s + want_r) & mask == (2 * oracle.dot(Xw[:, 0], Xw[:, 1], bits)) & mask
+    oracle.lib.p1o_ot_session_free(ss)
+    p1lib.p1_cot_free(snd); p1lib.p1_cot_free(rcv)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+# ---------------------------------------------------------------------------
+def _box(p1lib, c, **kw):
+    from linreg_mpc_b200 import phase1
+    return phase1.Phase1Box(p1lib, c["n"], c["d"], c["col_start"], c["precision"], c["precision_p2"],
+                            c["bits_p1"], c["bits_p2"], **kw)
+
+
+def test_whole_phase1_matches_reference_golden(p1lib, golden):
+    """every share word of every party equals the reference's own phase1.c output
+    (README example + synthetic instances; masking and OT; 64/64, 32/32, 64/32)"""
+    for c in golden["cases"]:
+        box = _box(p1lib, c, batch_pairs=3)
+        if c["use_ot"]:
+            got = box.run_ot(c["X"], c["y"], golden["ot_key"])
+        else:
+            got = box.run_masking(c["X"], c["y"], golden["ti_key"])
+            assert np.array_equal(got, c["shares"]), ("masking", c["instance"], c["bits_p1"], c["bits_p2"])
+            got = box.run_masking(c["X"], c["y"], golden["ti_key"], seeded=True)  # CSP-seeded masks: same words
+        assert np.array_equal(got, c["shares"]), (c["instance"], c["bits_p1"], c["bits_p2"], c["use_ot"])
+        box.close()
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+def test_whole_phase1_random_instance(p1lib, oracle, b1, b2, prec, prec2):
+    n, d, cs = 5000, 24, [0, 7, 15]
+    X, y, _ = po.generate_lin_regression(n, d, seed=21)
+    want = oracle.run(X, y, cs, prec, prec2, b1, b2, False, threads=8)
+    from linreg_mpc_b200 import phase1
+    box = phase1.Phase1Box(p1lib, n, d, cs, prec, prec2, b1, b2, batch_pairs=16)
+    got = box.run_masking(X, y, po.TI_KEY)
+    assert np.array_equal(got, want)
+    assert box.launches() > 0
+    box.close()
+
+
+def test_row_shards_combine_exactly(p1lib, oracle):
+    """two row shards (as two ranks would hold them) + wrapping u64 sum == unsharded run"""
+    from linreg_mpc_b200 import phase1
+    n, d, cs = 3000, 10, [0, 4, 7]
+    X, y, _ = po.generate_lin_regression(n, d, seed=31)
+    want = oracle.run(X, y, cs, 56, threads=4)
+    cut = 1280
+    boxes = [phase1.Phase1Box(p1lib, n, d, cs, 56, row0=0, n_rows=cut, batch_pairs=8),
+             phase1.Phase1Box(p1lib, n, d, cs, 56, row0=cut, n_rows=n - cut, batch_pairs=8)]
+    for b, (lo, hi) in zip(boxes, [(0, cut), (cut, n)]):
+        b.reset()
+        b.encode(np.ascontiguousarray(X[lo:hi]), np.ascontiguousarray(y[lo:hi]))
+        b.local_blocks()
+        b.cross_pairs_masking(po.TI_KEY)
+        b.sync()
+    boxes[0].flat += boxes[1].flat  # what the all-reduce does
+    boxes[0].torch.cuda.synchronize()
+    boxes[0].apply_values()
+    got = boxes[0].finalize()
+    assert np.array_equal(got, want)
+    for b in boxes:
+        b.close()

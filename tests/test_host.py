@@ -1,0 +1,85 @@
+"""CPU suite, part 2: host-side logic of the package (schedule, index maps) against the
+oracle, and the C-ABI library's exported surface.  No compute calls (no GPU here)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import linreg_mpc_b200 as pkg
+from linreg_mpc_b200 import ffi, phase1
+from oracle import pyoracle as po
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("d,cs", [(5, [0, 1, 2]), (12, [0, 3, 7]), (9, [0, 2, 4, 6]), (7, [0]), (6, [0, 3, 3]),
+                                  (100, [0, 33, 66])])
+def test_schedule_matches_oracle(oracle, d, cs):
+    s = phase1.Schedule(d, cs)
+    o = oracle.schedule(d, cs)
+    assert np.array_equal(s.i, o["i"]) and np.array_equal(s.j, o["j"])
+    assert np.array_equal(s.owner_i, o["owner_i"]) and np.array_equal(s.owner_j, o["owner_j"])
+    assert np.array_equal(s.kind, o["kind"])
+    assert np.array_equal(np.flatnonzero(s.kind == 2), s.cross)
+    # slots: idx(i,j) for feature rows, nA + j for the target row (src/phase1.c:581-585)
+    nA = d * (d + 1) // 2
+    for t in range(len(s.i)):
+        i, j = int(s.i[t]), int(s.j[t])
+        want = oracle.lib.p1o_idx(i, j) if i < d else nA + j
+        assert s.slot[t] == want
+
+
+def test_idx_is_symmetric_and_packed():
+    i = np.array([0, 3, 1, 499]); j = np.array([0, 1, 3, 498])
+    assert list(phase1.idx(i, j)) == [0, 7, 7, 499 * 500 // 2 + 498]
+
+
+def test_owner_rule_target_goes_to_last_provider():
+    assert list(phase1.owners([0, 1, 2, 3, 4, 5], [0, 1, 2])) == [0, 1, 2, 2, 2, 2]
+    with pytest.raises(ValueError):
+        phase1.owners([0], [3, 1])
+
+
+def test_ring_mac_count():
+    s = phase1.Schedule(500, po.even_col_start(500, 5))
+    assert s.num_cross == 100400
+    assert s.ring_macs(10 ** 6) == 10 ** 6 * (24850 + 3 * 100400)
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    pkg.build()
+    lib = pkg.P1Lib()
+    header = open(os.path.join(ROOT, "include", "p1gpu.h")).read()
+    declared = set(re.findall(r"\b(p1_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(ffi.SIGNATURES), declared ^ set(ffi.SIGNATURES)
+    raw = ctypes.CDLL(lib.path)
+    for name in sorted(declared):
+        assert getattr(raw, name) is not None
+
+
+def test_no_cpu_fallback_without_gpu():
+    """the product path fails loudly when no CUDA device is visible"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = pkg.P1Lib()
+    ctx = ctypes.c_void_p()
+    assert lib.p1_ctx_create(0, 64, 64, ctypes.byref(ctx)) == 1
+    assert b"no CUDA device" in lib.lib.p1_last_error()
+    with pytest.raises(ffi.P1Error):
+        lib.check(lib.p1_ctx_create(0, 64, 64, ctypes.byref(ctx)))
+
+
+def test_missing_library_raises():
+    with pytest.raises(ffi.P1Error):
+        pkg.P1Lib("/nonexistent/libp1gpu.so")
+
+
+def test_product_package_does_not_import_oracle():
+    for root, _, files in os.walk(os.path.join(ROOT, "linreg-mpc_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".c", ".h", ".cpp")):
+                text = open(os.path.join(root, f)).read()
+                assert "pyoracle" not in text and "liboracle" not in text and "p1_oracle" not in text, f
