@@ -50,6 +50,31 @@ void *p1_ctx_stream(p1_ctx *ctx);
 /* number of kernels this context has launched so far */
 uint64_t p1_ctx_launches(p1_ctx *ctx);
 
+/* Per-kernel-class device timing for bench.py's roofline line: while enabled, every
+ * kernel launch of this context is bracketed by CUDA events on the context's stream.
+ * p1_ctx_profile_read synchronises the stream, adds the elapsed times recorded since
+ * the last read to the per-class totals and returns the totals of `kernel_class`. */
+enum {
+	P1_K_ENCODE = 0,      /* k_rows_to_cols / k_vec_encode */
+	P1_K_LAYOUT,          /* k_cols_to_rows, word import/export */
+	P1_K_DIAG,            /* k_diag_stats / k_diag_seq */
+	P1_K_GRAM_IMAD,       /* k_gram_imad */
+	P1_K_GRAM_LIMBS,      /* k_limb_split (operand planes of the tensor-core Gram) */
+	P1_K_GRAM_TC,         /* k_gram_tc (tcgen05 kind::i8) */
+	P1_K_TI,              /* k_ti_generate */
+	P1_K_PARTY_B_MASK,    /* k_party<0> */
+	P1_K_PARTY_A_STEP,    /* k_party<1> */
+	P1_K_PARTY_B_SHARE,   /* k_party<2> */
+	P1_K_COT_RECV,        /* k_cot_tiles<receiver> */
+	P1_K_COT_SEND,        /* k_cot_tiles<sender> */
+	P1_K_COT_FINISH,      /* k_cot_finish */
+	P1_K_MISC,            /* k_acc_sub, k_ti_values */
+	P1_K_COUNT
+};
+int p1_ctx_profile(p1_ctx *ctx, int enable);
+int p1_ctx_profile_read(p1_ctx *ctx, int kernel_class, double *ms_total, uint64_t *launches);
+const char *p1_kernel_class_name(int kernel_class);
+
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
 int p1_dev_free(p1_ctx *ctx, void *dev);
 int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes);

@@ -274,6 +274,7 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 	P1_CHECK(per_sm > 0, "k_cot_tiles does not fit on an SM");
 	uint64_t cap = (uint64_t) ctx->sm_count * per_sm;
 	if(grid > cap) grid = cap;
+	p1_prof_begin(ctx, ROLE == 0 ? P1_K_COT_RECV : P1_K_COT_SEND);
 	if(s->bits == 64) k_cot_tiles<uint64_t, ROLE><<<(unsigned) grid, COT_THREADS, smem, ctx->stream>>>(P);
 	else k_cot_tiles<uint32_t, ROLE><<<(unsigned) grid, COT_THREADS, smem, ctx->stream>>>(P);
 	P1_LAUNCHED(ctx);
@@ -305,6 +306,7 @@ extern "C" int p1_cot_receiver_finish(p1_ctx *ctx, p1_cot *r, const void *c_dev,
 	uint64_t m = (uint64_t) r->n_rows * (uint64_t) r->bits;
 	unsigned grid = (unsigned) ((m + 256 * 8 - 1) / (256 * 8));
 	if(grid > (unsigned) ctx->sm_count * 8) grid = ctx->sm_count * 8;
+	p1_prof_begin(ctx, P1_K_COT_FINISH);
 	if(r->bits == 64) k_cot_finish<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) r->pads, (const uint64_t *) c_dev, (const uint64_t *) r->col_ptr, m, acc_dev + slot);
 	else k_cot_finish<uint32_t><<<grid, 256, 0, ctx->stream>>>((const uint32_t *) r->pads, (const uint32_t *) c_dev, (const uint32_t *) r->col_ptr, m, acc_dev + slot);
 	P1_LAUNCHED(ctx);

@@ -5,6 +5,7 @@
 //   k_vec_encode   : same for the target vector (src/linear.c:83-87).
 //   k_cols_to_rows : column-major -> the reference's row-major layout (tests / download).
 #include "p1_common.cuh"
+#include <type_traits>
 
 // (fixed_t) cast with x86 cvttsd2si semantics: truncate toward zero, INT_MIN of the
 // target width when out of range or NaN ("integer indefinite").  CUDA's cvt.rzi
@@ -154,6 +155,7 @@ __global__ void __launch_bounds__(256) k_cols_to_rows(const W *__restrict__ xt, 
 template <typename W, typename SRC>
 static int launch_rows_to_cols(p1_ctx *ctx, const SRC *src, size_t rows, size_t d, size_t row_off, p1_data *out, EncodeParams ep) {
 	dim3 grid((unsigned) ((d + 31) / 32), (unsigned) ((rows + ENC_ROWS_PER_CTA - 1) / ENC_ROWS_PER_CTA)), block(32, 8);
+	p1_prof_begin(ctx, std::is_same<SRC, double>::value ? P1_K_ENCODE : P1_K_LAYOUT);
 	k_rows_to_cols<W, SRC><<<grid, block, 0, ctx->stream>>>(src, rows, d, row_off, (W *) out->xt, out->ld, out->stats, ep);
 	P1_LAUNCHED(ctx);
 	return 0;
@@ -163,6 +165,7 @@ template <typename W, typename SRC>
 static int launch_vec(p1_ctx *ctx, const SRC *src, p1_data *out, EncodeParams ep) {
 	unsigned blocks = (unsigned) ((out->n + 256 * 8 - 1) / (256 * 8));
 	if(blocks > (unsigned) ctx->sm_count * 8) blocks = ctx->sm_count * 8;
+	p1_prof_begin(ctx, std::is_same<SRC, double>::value ? P1_K_ENCODE : P1_K_LAYOUT);
 	k_vec_encode<W, SRC><<<blocks, 256, 0, ctx->stream>>>(src, out->n, (W *) out->xt + out->d * out->ld, out->stats + 4 * out->d, ep);
 	P1_LAUNCHED(ctx);
 	return 0;
@@ -198,6 +201,7 @@ int p1_launch_words_out(p1_ctx *ctx, const p1_data *dt, void *Xw, void *yw) {
 	size_t w = (size_t) dt->bits / 8;
 	if(Xw) {
 		dim3 grid((unsigned) ((dt->d + 31) / 32), (unsigned) ((dt->n + 31) / 32)), block(32, 8);
+		p1_prof_begin(ctx, P1_K_LAYOUT);
 		if(dt->bits == 64) k_cols_to_rows<uint64_t><<<grid, block, 0, ctx->stream>>>((const uint64_t *) dt->xt, dt->ld, dt->n, dt->d, (uint64_t *) Xw);
 		else k_cols_to_rows<uint32_t><<<grid, block, 0, ctx->stream>>>((const uint32_t *) dt->xt, dt->ld, dt->n, dt->d, (uint32_t *) Xw);
 		P1_LAUNCHED(ctx);

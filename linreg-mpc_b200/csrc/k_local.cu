@@ -17,6 +17,7 @@ __global__ void k_diag_stats(const uint64_t *__restrict__ stats, size_t col_lo, 
 
 int p1_launch_diag_stats(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, uint64_t *acc_dev) {
 	size_t m = col_hi - col_lo;
+	p1_prof_begin(ctx, P1_K_DIAG);
 	k_diag_stats<<<(unsigned) ((m + 127) / 128), 128, 0, ctx->stream>>>(data->stats, col_lo, m, data->d, p1_nA(data->d), acc_dev);
 	P1_LAUNCHED(ctx);
 	return 0;
@@ -55,6 +56,7 @@ int p1_launch_diag_seq(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t c
 	size_t m = col_hi - col_lo;
 	double scale = (double) (1ll << precision), inv = 1.0 / scale; // both exact powers of two
 	unsigned blocks = (unsigned) ((m + 31) / 32);
+	p1_prof_begin(ctx, P1_K_DIAG);
 	if(data->bits == 64) k_diag_seq<uint64_t><<<blocks, 32, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, data->n, col_lo, m, inv, scale, xy_dev);
 	else k_diag_seq<uint32_t><<<blocks, 32, 0, ctx->stream>>>((const uint32_t *) data->xt, data->ld, data->n, col_lo, m, inv, scale, xy_dev);
 	P1_LAUNCHED(ctx);
@@ -185,6 +187,7 @@ int p1_launch_gram_imad(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t 
 	unsigned slices = (unsigned) ((gs.n + rows_per_cta - 1) / rows_per_cta);
 	size_t smem = 2 * GI_T * (128 + 1) * sizeof(uint32_t); // == 2*64*65*8 for the wide path
 	dim3 grid((unsigned) pairs, slices);
+	p1_prof_begin(ctx, P1_K_GRAM_IMAD);
 	if(data->bits == 64) {
 		P1_CUDA(cudaFuncSetAttribute(k_gram_imad<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 		k_gram_imad<uint64_t><<<grid, GI_THREADS, smem, ctx->stream>>>((const uint64_t *) data->xt, data->stats, gs, rows_per_cta, acc_dev);

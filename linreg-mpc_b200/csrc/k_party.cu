@@ -105,6 +105,7 @@ static int launch_party(p1_ctx *ctx, const p1_data *data, const int32_t *cols, c
 	if(p1_small_to_dev(ctx, cols, count * sizeof(int32_t), 0, &cols_d)) return 1;
 	if(MODE != 0 && p1_small_to_dev(ctx, slots, count * sizeof(int64_t), 1, &slots_d)) return 1;
 	dim3 grid((unsigned) ((data->n + PK_CHUNK - 1) / PK_CHUNK), (unsigned) count);
+	p1_prof_begin(ctx, MODE == 0 ? P1_K_PARTY_B_MASK : MODE == 1 ? P1_K_PARTY_A_STEP : P1_K_PARTY_B_SHARE);
 	if(data->bits == 64) {
 		k_party<uint64_t, MODE><<<grid, PK_THREADS, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, data->n,
 			(const int32_t *) cols_d, (const int64_t *) slots_d, (const uint64_t *) T, ld_T, (const uint64_t *) in, ld_in,
@@ -147,6 +148,7 @@ extern "C" int p1_acc_sub_values(p1_ctx *ctx, uint64_t *acc_dev, const int64_t *
 	P1_CHECK(acc_dev && slots && value_dev, "p1_acc_sub_values: arguments may not be null");
 	const void *slots_d = NULL;
 	if(p1_small_to_dev(ctx, slots, count * sizeof(int64_t), 1, &slots_d)) return 1;
+	p1_prof_begin(ctx, P1_K_MISC);
 	k_acc_sub<<<(unsigned) ((count + 255) / 256), 256, 0, ctx->stream>>>(acc_dev, (const int64_t *) slots_d, value_dev, count);
 	P1_LAUNCHED(ctx);
 	return 0;
@@ -158,6 +160,7 @@ extern "C" int p1_ti_values(p1_ctx *ctx, const uint64_t *xy_dev, const uint64_t 
 	if(!count) return 0;
 	P1_CHECK(xy_dev && r_dev && value_a_dev && value_b_dev, "p1_ti_values: arguments may not be null");
 	uint64_t mask = ctx->bits_p1 == 64 ? ~0ull : 0xffffffffull;
+	p1_prof_begin(ctx, P1_K_MISC);
 	k_ti_values<<<(unsigned) ((count + 255) / 256), 256, 0, ctx->stream>>>(xy_dev, r_dev, count, mask, value_a_dev, value_b_dev);
 	P1_LAUNCHED(ctx);
 	return 0;

@@ -210,6 +210,7 @@ static int launch_ti(p1_ctx *ctx, const TiParams &P, bool aligned) {
 	uint64_t grid = (uint64_t) ctx->sm_count * blocks_per_sm;
 	uint64_t need = (units + 15) / 16; // 16 warps per CTA
 	if(grid > need) grid = need;
+	p1_prof_begin(ctx, P1_K_TI);
 	if(aligned) k_ti_generate<W, REPL, NTAB, true><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
 	else k_ti_generate<W, REPL, NTAB, false><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
 	P1_LAUNCHED(ctx);

@@ -69,6 +69,9 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->stage_bytes = 0;
 	ctx->limb_ws = NULL;
 	ctx->limb_ws_bytes = 0;
+	ctx->prof = false;
+	ctx->prof_open = -1;
+	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
 	if(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
 	   cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming) != cudaSuccess ||
 	   cudaMallocHost(&ctx->pin, ctx->pin_bytes) != cudaSuccess ||
@@ -91,6 +94,8 @@ extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 		}
 	}
 	if(ctx->limb_ws) cudaFree(ctx->limb_ws);
+	for(auto &r : ctx->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+	for(auto e : ctx->prof_pool) cudaEventDestroy(e);
 	cudaFree(ctx->scratch);
 	cudaFreeHost(ctx->pin);
 	cudaEventDestroy(ctx->ev);
@@ -122,6 +127,65 @@ extern "C" int p1_ctx_wait(p1_ctx *waiter, p1_ctx *signaler) {
 
 extern "C" void *p1_ctx_stream(p1_ctx *ctx) { return ctx ? (void *) ctx->stream : NULL; }
 extern "C" uint64_t p1_ctx_launches(p1_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+// ------------------------------------------------------------------ profiling
+
+static cudaEvent_t prof_event(p1_ctx *ctx) {
+	cudaEvent_t e = NULL;
+	if(!ctx->prof_pool.empty()) {
+		e = ctx->prof_pool.back();
+		ctx->prof_pool.pop_back();
+	} else {
+		cudaEventCreate(&e);
+	}
+	return e;
+}
+
+void p1_prof_begin(p1_ctx *ctx, int cls) {
+	if(!ctx->prof) return;
+	ctx->prof_open = cls;
+	ctx->prof_a = prof_event(ctx);
+	cudaEventRecord(ctx->prof_a, ctx->stream);
+}
+
+void p1_prof_end(p1_ctx *ctx) {
+	if(!ctx->prof || ctx->prof_open < 0) return;
+	cudaEvent_t b = prof_event(ctx);
+	cudaEventRecord(b, ctx->stream);
+	ctx->prof_recs.push_back({ctx->prof_open, ctx->prof_a, b});
+	ctx->prof_open = -1;
+}
+
+static const char *const K_NAMES[P1_K_COUNT] = {"encode", "layout", "diag", "gram_imad", "gram_limbs", "gram_tc", "ti_generate",
+	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc"};
+
+extern "C" const char *p1_kernel_class_name(int c) { return c >= 0 && c < P1_K_COUNT ? K_NAMES[c] : NULL; }
+
+extern "C" int p1_ctx_profile(p1_ctx *ctx, int enable) {
+	P1_ENTER(ctx);
+	ctx->prof = enable != 0;
+	ctx->prof_open = -1;
+	return 0;
+}
+
+extern "C" int p1_ctx_profile_read(p1_ctx *ctx, int cls, double *ms_total, uint64_t *launches) {
+	P1_ENTER(ctx);
+	P1_CHECK(cls >= 0 && cls < P1_K_COUNT, "p1_ctx_profile_read: unknown kernel class %d", cls);
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	for(auto &r : ctx->prof_recs) {
+		float ms = 0;
+		if(cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+			ctx->prof_ms[r.cls] += ms;
+			ctx->prof_n[r.cls]++;
+		}
+		ctx->prof_pool.push_back(r.a);
+		ctx->prof_pool.push_back(r.b);
+	}
+	ctx->prof_recs.clear();
+	if(ms_total) *ms_total = ctx->prof_ms[cls];
+	if(launches) *launches = ctx->prof_n[cls];
+	return 0;
+}
 
 extern "C" int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev) {
 	P1_ENTER(ctx);

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include <mutex>
+#include <vector>
 #include "../../include/p1gpu.h"
 
 #define P1_SQ_LIMIT_BITS 26   // |word| < 2^26  =>  v*v exact in binary64 (p1gpu.h, p1_finalize)
@@ -25,7 +26,20 @@ struct p1_ctx {
 	void *stage[2]; size_t stage_bytes; cudaEvent_t stage_ev[2];
 	// tcgen05 Gram workspace (limb planes), grown on demand
 	void *limb_ws;  size_t limb_ws_bytes;
+	// per-kernel-class event timing (p1_ctx_profile)
+	bool prof;
+	int prof_open;                       // class of the launch being bracketed, -1 if none
+	cudaEvent_t prof_a;
+	struct ProfRec { int cls; cudaEvent_t a, b; };
+	std::vector<ProfRec> prof_recs;
+	std::vector<cudaEvent_t> prof_pool;
+	double prof_ms[P1_K_COUNT];
+	uint64_t prof_n[P1_K_COUNT];
 };
+
+// call right before a kernel launch; P1_LAUNCHED closes the bracket
+void p1_prof_begin(p1_ctx *ctx, int cls);
+void p1_prof_end(p1_ctx *ctx);
 
 struct p1_data {
 	int device, bits;
@@ -41,7 +55,7 @@ int p1_fail(const char *fmt, ...);
 #define P1_CHECK(cond, ...) do { if(!(cond)) return p1_fail(__VA_ARGS__); } while(0)
 #define P1_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) \
 	return p1_fail("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while(0)
-#define P1_LAUNCHED(ctx) do { (ctx)->launches++; cudaError_t e_ = cudaGetLastError(); if(e_ != cudaSuccess) \
+#define P1_LAUNCHED(ctx) do { (ctx)->launches++; p1_prof_end(ctx); cudaError_t e_ = cudaGetLastError(); if(e_ != cudaSuccess) \
 	return p1_fail("%s:%d: kernel launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); } while(0)
 
 static inline size_t p1_round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }

@@ -18,6 +18,9 @@ c_d = ctypes.c_double
 c_cp = ctypes.c_char_p
 
 P1_GRAM_AUTO, P1_GRAM_IMAD, P1_GRAM_TCGEN05 = 0, 1, 2
+# kernel classes of p1_ctx_profile_read (enum in include/p1gpu.h)
+(P1_K_ENCODE, P1_K_LAYOUT, P1_K_DIAG, P1_K_GRAM_IMAD, P1_K_GRAM_LIMBS, P1_K_GRAM_TC, P1_K_TI, P1_K_PARTY_B_MASK,
+ P1_K_PARTY_A_STEP, P1_K_PARTY_B_SHARE, P1_K_COT_RECV, P1_K_COT_SEND, P1_K_COT_FINISH, P1_K_MISC, P1_K_COUNT) = range(15)
 
 # every symbol include/p1gpu.h declares, with its signature
 SIGNATURES = {
@@ -28,6 +31,9 @@ SIGNATURES = {
     "p1_ctx_wait": (c_i, [c_vp, c_vp]),
     "p1_ctx_stream": (c_vp, [c_vp]),
     "p1_ctx_launches": (c_u64, [c_vp]),
+    "p1_ctx_profile": (c_i, [c_vp, c_i]),
+    "p1_ctx_profile_read": (c_i, [c_vp, c_i, ctypes.POINTER(c_d), ctypes.POINTER(c_u64)]),
+    "p1_kernel_class_name": (c_cp, [c_i]),
     "p1_dev_alloc": (c_i, [c_vp, c_sz, ctypes.POINTER(c_vp)]),
     "p1_dev_free": (c_i, [c_vp, c_vp]),
     "p1_dev_zero": (c_i, [c_vp, c_vp, c_sz]),

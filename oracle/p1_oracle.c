@@ -461,3 +461,25 @@ int p1o_run(const double *X, const double *y, size_t n, size_t d, int num_dp, co
 	free(rc.kind);
 	return 0;
 }
+
+/* ---------------- instance files (bench.py cpu_baseline leg) ----------------
+ * Writes X, y in the input-file format parsed by src/config.c:24-44 and
+ * src/linear.c:27-102 (layout of experiments/generate_tests.py:41-74); %.17g
+ * round-trips every double through the reference's fscanf("%lf"). */
+#include <stdio.h>
+int p1o_write_instance(const char *path, const double *X, const double *y, size_t n, size_t d,
+	int num_dp, const int64_t *col_start) {
+	FILE *f = fopen(path, "w");
+	if(!f) return 1;
+	static char buf[1 << 20];
+	setvbuf(f, buf, _IOFBF, sizeof(buf));
+	fprintf(f, "%zu %zu %d\nlocalhost:1234\nlocalhost:1235\n", n, d, num_dp);
+	for(int k = 0; k < num_dp; k++) fprintf(f, "localhost:%d %lld\n", 1236 + k, (long long) col_start[k]);
+	fprintf(f, "%zu %zu\n", n, d);
+	for(size_t i = 0; i < n; i++) {
+		for(size_t j = 0; j < d; j++) fprintf(f, j + 1 < d ? "%.17g " : "%.17g\n", X[i * d + j]);
+	}
+	fprintf(f, "%zu\n", n);
+	for(size_t i = 0; i < n; i++) fprintf(f, i + 1 < n ? "%.17g " : "%.17g\n", y[i]);
+	return fclose(f) ? 1 : 0;
+}

@@ -88,6 +88,8 @@ class Oracle:
         L.p1o_run.argtypes = [c_vp, c_vp, c_sz, c_sz, c_i, c_vp, c_i, c_i, c_i, c_i, c_i,
                               c_u8p, c_u8p, c_i, c_vp, c_vp, c_vp]
         L.p1o_run.restype = c_i
+        L.p1o_write_instance.argtypes = [c_u8p, c_vp, c_vp, c_sz, c_sz, c_i, c_vp]
+        L.p1o_write_instance.restype = c_i
         L.aes128_set_key.argtypes = [c_vp, c_u8p]
         L.aes128_force_portable.argtypes = [c_vp]
         L.aes128_ctr_keystream.argtypes = [c_vp, c_u64, c_vp, c_sz]
@@ -141,6 +143,12 @@ class Oracle:
         self.lib.p1o_ot_inner_product(session, _ptr(xs), 1, _ptr(xr), 1, n, bits,
                                       ctypes.byref(ss), ctypes.byref(sr), _ptr(u), _ptr(c))
         return (ss.value, sr.value, u, c) if want_wire else (ss.value, sr.value)
+
+    def write_instance(self, path, X, y, col_start):
+        """fast C writer of the reference's input-file format (same text as write_instance below)"""
+        X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        cs = np.ascontiguousarray(col_start, dtype=np.int64)
+        assert self.lib.p1o_write_instance(path.encode(), _ptr(X), _ptr(y), X.shape[0], X.shape[1], len(cs), _ptr(cs)) == 0
 
     def run(self, X, y, col_start, precision, precision_p2=0, bits_p1=64, bits_p2=64, use_ot=False,
             ti_key=TI_KEY, ot_key=OT_KEY, threads=1, want_encoded=False):
