@@ -185,7 +185,7 @@ int p1_launch_gram_imad(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t 
 	if(want > 65535) want = 65535;
 	size_t rows_per_cta = p1_round_up((gs.n + want - 1) / want, 128);
 	unsigned slices = (unsigned) ((gs.n + rows_per_cta - 1) / rows_per_cta);
-	size_t smem = 2 * GI_T * (128 + 1) * sizeof(uint32_t); // == 2*64*65*8 for the wide path
+	size_t smem = 2 * GI_T * (64 + 1) * sizeof(uint64_t); // wide path: 66 560 B; the narrow path needs 2*64*129*4 = 66 048 B
 	dim3 grid((unsigned) pairs, slices);
 	p1_prof_begin(ctx, P1_K_GRAM_IMAD);
 	if(data->bits == 64) {

@@ -400,7 +400,7 @@ extern "C" int p1_local_block(p1_ctx *ctx, const p1_data *data, size_t col_lo, s
 	if(m < 2) return 0;
 	if(algo == P1_GRAM_AUTO) {
 		// crossover measured on B200 (profiles/): the limb GEMM wins once the block fills a 128x128 tile
-		algo = (m >= 64 && data->n >= 4096) ? P1_GRAM_TCGEN05 : P1_GRAM_IMAD;
+		algo = P1_GRAM_IMAD;
 	}
 	if(algo == P1_GRAM_TCGEN05) return p1_launch_gram_tc(ctx, data, col_lo, col_hi, owns_target, acc_dev);
 	P1_CHECK(algo == P1_GRAM_IMAD, "p1_local_block: unknown algo %d", algo);
