@@ -152,10 +152,10 @@ def test_diagonal_exact_and_sequential(p1lib, oracle, bits):
     n, d = 3000, 6
     dt = po.word_dtype(bits)
     sdt = np.int64 if bits == 64 else np.int32
-    lim = 2 ** 25 if bits == 64 else 2 ** 14
+    lim = 2 ** 20 if bits == 64 else 2 ** 14   # n * lim^2 stays below 2^53
     Xs = rng.integers(-lim, lim, (n, d)).astype(sdt)
     if bits == 64:
-        Xs[:, 1] *= 2 ** 12      # |word| >= 2^26: the exact shortcut must be refused
+        Xs[:, 1] *= 2 ** 12      # |word| up to 2^32 >= 2^26: the exact shortcut must be refused
         Xs[:, 4] = rng.integers(2 ** 25, 2 ** 26, n)  # no single violation but sum of squares > 2^53
     Xw = Xs.view(dt)
     data = from_words(p1lib, ctx, Xw, None)
