@@ -75,6 +75,13 @@ int p1_ctx_profile(p1_ctx *ctx, int enable);
 int p1_ctx_profile_read(p1_ctx *ctx, int kernel_class, double *ms_total, uint64_t *launches);
 const char *p1_kernel_class_name(int kernel_class);
 
+/* Tuning knobs (0 = built-in choice).  Used by the parity tests to force the multi-chunk
+ * and multi-slice paths at small sizes, and by bench.py sweeps.
+ *   "gram_tc_max_slices"   : upper bound on the row slices (grid.y) of k_gram_tc
+ *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
+ *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on */
+int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
+
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
 int p1_dev_free(p1_ctx *ctx, void *dev);
 int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes);

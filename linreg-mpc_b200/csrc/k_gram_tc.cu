@@ -1,6 +1,444 @@
-// placeholder until the tcgen05 kernel lands
+// Ring Gram of a column block on the 5th-gen tensor cores (tcgen05 kind::i8).
+//
+// Replaces the "own both" pair loop of src/phase1.c:569-571 (inner_product_local,
+// :14-20) for a whole column block at once:  acc[idx(i,j)] += sum_k X[k][i]*X[k][j]
+// mod 2^64 (mod 2^32 lives in the low half).
+//
+// Arithmetic.  Every ring word is read as a signed integer and split into L balanced
+// base-256 digits  x = sum_l x_l 256^l,  x_l in [-128,127]  (k_limb_split; L is chosen
+// from the per-column max |word| gathered by the encode pass; for L = W/8 the dropped
+// carry is a multiple of 2^W, so full-range words are exact mod 2^W as well).  Then
+//     x*y = sum_{l,m} x_l*y_m * 256^(l+m)                       (mod 2^W: l+m < W/8)
+// is a set of s8 x s8 -> s32 GEMMs.  Products are grouped by shift s = l+m into one
+// s32 TMEM accumulator each; a group receives at most L products per row, each
+// |.| <= 2^14, so after at most floor((2^17-1)/L) rows the accumulators are drained
+// into 64-bit registers (sum_s acc_s << 8s), which keeps every s32 sum exact.
+//
+// Data path.  k_limb_split writes digit planes P[l][col][row] (K-major: the contraction
+// index k = row is contiguous).  One CTA owns a 128 x 64 block of the (column x column)
+// output and a slice of the rows:
+//   warp 0    TMA producer: box (128 rows, 128|64 cols, L limbs) -> smem, SWIZZLE_128B
+//   warp 1    MMA issuer:   for each K-step of 32 rows and each A-limb l one
+//             tcgen05.mma  D[:, 64l .. 64(l+c)) += A_l (128 x 32) * [B_0;..;B_{c-1}]^T
+//             (the B limb tiles are stacked in smem, so N = 64c covers c shift groups)
+//   warps 2-5 epilogue: tcgen05.ld the groups, recombine into u64 registers, zero TMEM
+//             for the next chunk; at the end red.global.add.u64 into the packed share.
 #include "p1_common.cuh"
+#include <cuda.h>
+
+#define TC_THREADS 192
+#define TC_BM 128          // output rows per CTA   (A operand columns of X)
+#define TC_BN 64           // output columns per CTA (B operand columns of X)
+#define TC_BK 128          // rows of X per pipeline stage (= one 128-byte swizzle row of s8)
+#define TC_A_BYTES (TC_BM * TC_BK)
+#define TC_B_BYTES (TC_BN * TC_BK)
+
+struct TcSet {
+	size_t col_lo;
+	int mc, m;            // feature columns; + target
+	size_t d, nA;
+};
+
+// accumulator slot of the pair (a > b) of the set (src/phase1.c:581-585)
+__device__ __forceinline__ size_t tc_slot(const TcSet &gs, int a, int b) {
+	size_t j = gs.col_lo + b;
+	if(a >= gs.mc) return gs.nA + j;
+	size_t i = gs.col_lo + a;
+	return i * (i + 1) / 2 + j;
+}
+
+// ------------------------------------------------------------------ digit planes
+
+// grid (ceil(ldp/1024), m), block 256: thread = 4 consecutive rows of one column
+template <typename W>
+__global__ void __launch_bounds__(256) k_limb_split(const W *__restrict__ xt, size_t ld, TcSet gs, int L,
+	uint8_t *__restrict__ planes, size_t ldp, size_t plane_stride) {
+	typedef typename p1_word<W>::s S;
+	size_t r = ((size_t) blockIdx.x * 256 + threadIdx.x) * 4;
+	if(r >= ldp) return;
+	int a = blockIdx.y;
+	size_t c = a < gs.mc ? gs.col_lo + a : gs.d;
+	const W *src = xt + c * ld + r;
+	int64_t v[4];
+	if(r < ld) {
+		if(sizeof(W) == 8) {
+			ulonglong2 p0 = *reinterpret_cast<const ulonglong2 *>(src), p1 = *reinterpret_cast<const ulonglong2 *>(src + 2);
+			v[0] = (int64_t) p0.x; v[1] = (int64_t) p0.y; v[2] = (int64_t) p1.x; v[3] = (int64_t) p1.y;
+		} else {
+			uint4 p = *reinterpret_cast<const uint4 *>(src);
+			v[0] = (S) p.x; v[1] = (S) p.y; v[2] = (S) p.z; v[3] = (S) p.w;
+		}
+	} else {
+		v[0] = v[1] = v[2] = v[3] = 0;
+	}
+	uint8_t *dst = planes + (size_t) a * ldp + r;
+	for(int l = 0; l < L; l++) {
+		uint32_t packed = 0;
+#pragma unroll
+		for(int u = 0; u < 4; u++) {
+			int64_t dg = (int64_t) (int8_t) (v[u] & 0xff);
+			v[u] = (v[u] - dg) >> 8;
+			packed |= ((uint32_t) dg & 0xffu) << (8 * u);
+		}
+		*reinterpret_cast<uint32_t *>(dst + (size_t) l * plane_stride) = packed;
+	}
+}
+
+// ------------------------------------------------------------------ PTX wrappers
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+	uint32_t addr = smem_u32(bar);
+	asm volatile(
+		"{\n\t"
+		".reg .pred p;\n\t"
+		"WAIT_%=:\n\t"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+		"@p bra DONE_%=;\n\t"
+		"bra WAIT_%=;\n\t"
+		"DONE_%=:\n\t"
+		"}" ::"r"(addr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2) {
+	asm volatile(
+		"cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+		::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+		: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, s8 x s8 -> s32
+__device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+	asm volatile(
+		"{\n\t"
+		".reg .pred p;\n\t"
+		"setp.ne.b32 p, %4, 0;\n\t"
+		"tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t"
+		"}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u), "r"(0u), "r"(0u), "r"(0u)
+		: "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t (&v)[32]) {
+	asm volatile(
+		"tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+		"{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+		"%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+		: "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+		  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+		  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+		  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+		: "r"(addr));
+	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_zero32(uint32_t addr) {
+	const uint32_t z = 0;
+	asm volatile(
+		"tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+		"{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
+		"%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(addr), "r"(z) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor: 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
+	return (uint64_t) ((saddr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::i8 instruction descriptor: D = s32, A = B = s8, both K-major, M = 128
+__device__ __forceinline__ uint32_t tc_idesc(int N) {
+	return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
+}
+
+// ------------------------------------------------------------------ the GEMM kernel
+
+struct TcParams {
+	TcSet gs;
+	int L;                 // digits per word
+	int WD;                // ring bytes (8 or 4): pairs with l+m >= WD vanish mod 2^W
+	int G;                 // shift groups = min(2L-1, WD)
+	int stages;
+	uint32_t tmem_cols;    // power of two >= 64*G
+	int nblk;              // K-blocks (of TC_BK rows) in the shard
+	int blk_per_cta;       // K-blocks per CTA (grid.y slices)
+	int chunk_blks;        // K-blocks per exact s32 accumulation chunk
+	uint64_t *acc;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant__ CUtensorMap mapA,
+	const __grid_constant__ CUtensorMap mapB, const TcParams P) {
+	extern __shared__ __align__(1024) uint8_t smem_raw[];
+	__shared__ __align__(8) uint64_t bar_full[8], bar_empty[8], bar_tfull, bar_tempty;
+	__shared__ uint32_t tmem_base_s;
+
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int L = P.L, G = P.G, S = P.stages;
+	const uint32_t stage_bytes = (uint32_t) L * (TC_A_BYTES + TC_B_BYTES);
+	uint8_t *smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+
+	// tile decode: ta = 128-wide row tile, tb = 64-wide column tile with 64*tb < min(128*(ta+1), mc)
+	int ta = 0, tb = (int) blockIdx.x;
+	for(;;) {
+		int lim = TC_BM * (ta + 1) < P.gs.mc ? TC_BM * (ta + 1) : P.gs.mc;
+		int cnt = (lim + TC_BN - 1) / TC_BN;
+		if(tb < cnt) break;
+		tb -= cnt;
+		ta++;
+	}
+	const int blk_lo = (int) blockIdx.y * P.blk_per_cta;
+	const int blk_hi = blk_lo + P.blk_per_cta < P.nblk ? blk_lo + P.blk_per_cta : P.nblk;
+	const int nb = blk_hi - blk_lo;          // > 0 by construction of the grid
+
+	if(threadIdx.x == 0) {
+		for(int s = 0; s < S; s++) {
+			mbar_init(&bar_full[s], 1);
+			mbar_init(&bar_empty[s], 1);
+		}
+		mbar_init(&bar_tfull, 1);
+		mbar_init(&bar_tempty, 128);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+		asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+		asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+	}
+	if(warp == 1) {
+		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(P.tmem_cols) : "memory");
+		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+	}
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t tmem = tmem_base_s;
+
+	if(warp == 0) {
+		// ===== TMA producer
+		if(lane == 0) {
+			for(int b = 0; b < nb; b++) {
+				int s = b % S;
+				uint32_t ph = (uint32_t) (b / S) & 1u;
+				mbar_wait(&bar_empty[s], ph ^ 1u);
+				mbar_expect_tx(&bar_full[s], stage_bytes);
+				uint8_t *sa = smem + (size_t) s * stage_bytes, *sb = sa + (size_t) L * TC_A_BYTES;
+				int k0 = (blk_lo + b) * TC_BK;
+				tma_load_3d(sa, &mapA, &bar_full[s], k0, ta * TC_BM, 0);
+				tma_load_3d(sb, &mapB, &bar_full[s], k0, tb * TC_BN, 0);
+			}
+		}
+	} else if(warp == 1) {
+		// ===== MMA issuer (one thread)
+		if(lane == 0) {
+			uint32_t chunk = 0;
+			for(int b = 0; b < nb; b++) {
+				if(b % P.chunk_blks == 0) {
+					// the epilogue has drained and zeroed the accumulators of the previous chunk
+					mbar_wait(&bar_tempty, chunk & 1u);
+					tc_fence_after();
+				}
+				int s = b % S;
+				uint32_t ph = (uint32_t) (b / S) & 1u;
+				mbar_wait(&bar_full[s], ph);
+				tc_fence_after();
+				uint32_t sa = smem_u32(smem + (size_t) s * stage_bytes), sb = sa + (uint32_t) L * TC_A_BYTES;
+#pragma unroll
+				for(int k4 = 0; k4 < TC_BK / 32; k4++) {
+					for(int l = 0; l < L; l++) {
+						int cnt = L < P.WD - l ? L : P.WD - l;     // B limbs m with l+m < WD
+						if(cnt <= 0) break;
+						uint64_t da = tc_smem_desc(sa + (uint32_t) l * TC_A_BYTES + (uint32_t) k4 * 32);
+						int c0 = cnt < 4 ? cnt : 4;
+						tc_mma_i8(tmem + (uint32_t) (TC_BN * l), da, tc_smem_desc(sb + (uint32_t) k4 * 32), tc_idesc(TC_BN * c0), 1u);
+						if(cnt > 4)
+							tc_mma_i8(tmem + (uint32_t) (TC_BN * (l + 4)), da, tc_smem_desc(sb + 4u * TC_B_BYTES + (uint32_t) k4 * 32),
+								tc_idesc(TC_BN * (cnt - 4)), 1u);
+					}
+				}
+				tc_commit(&bar_empty[s]);          // frees the smem stage once these MMAs have read it
+				if((b + 1) % P.chunk_blks == 0 || b + 1 == nb) {
+					tc_commit(&bar_tfull);         // accumulators of this chunk are complete
+					chunk++;
+				}
+			}
+		}
+	} else {
+		// ===== epilogue: 4 warps, warp q = warp % 4 owns TMEM lanes [32q, 32q+32)
+		const int q = warp & 3;
+		const uint32_t tlane = tmem + ((uint32_t) (32 * q) << 16);
+		uint64_t out[TC_BN];
+#pragma unroll
+		for(int c = 0; c < TC_BN; c++) out[c] = 0;
+		for(int g = 0; g < 2 * G; g++) tmem_zero32(tlane + (uint32_t) (32 * g));
+		tmem_wait_st();
+		tc_fence_before();
+		mbar_arrive(&bar_tempty);
+		const int nchunks = (nb + P.chunk_blks - 1) / P.chunk_blks;
+		for(int ch = 0; ch < nchunks; ch++) {
+			mbar_wait(&bar_tfull, (uint32_t) ch & 1u);
+			tc_fence_after();
+#pragma unroll
+			for(int s = 0; s < 8; s++) {
+				if(s < G) {
+#pragma unroll
+					for(int h = 0; h < 2; h++) {
+						uint32_t v[32];
+						tmem_ld32(tlane + (uint32_t) (TC_BN * s + 32 * h), v);
+#pragma unroll
+						for(int c = 0; c < 32; c++) out[32 * h + c] += (uint64_t) (int64_t) (int32_t) v[c] << (8 * s);
+					}
+				}
+			}
+			if(ch + 1 < nchunks) {
+				for(int g = 0; g < 2 * G; g++) tmem_zero32(tlane + (uint32_t) (32 * g));
+				tmem_wait_st();
+				tc_fence_before();
+				mbar_arrive(&bar_tempty);
+			}
+		}
+		// row of the output tile = TMEM lane
+		const int a = ta * TC_BM + 32 * q + lane;
+		if(a < P.gs.m) {
+#pragma unroll
+			for(int c = 0; c < TC_BN; c++) {
+				int b = tb * TC_BN + c;
+				if(b < a && b < P.gs.mc) p1_red_add(P.acc + tc_slot(P.gs, a, b), out[c]);
+			}
+		}
+	}
+	tc_fence_before();
+	__syncthreads();
+	if(warp == 1) {
+		tc_fence_after();
+		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(P.tmem_cols) : "memory");
+	}
+}
+
+// ------------------------------------------------------------------ host side
+
+typedef CUresult (*tmap_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+	const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static tmap_encode_fn get_tmap_encode() {
+	static tmap_encode_fn fn = NULL;
+	if(!fn) {
+		void *p = NULL;
+		cudaDriverEntryPointQueryResult q;
+		if(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+			fn = (tmap_encode_fn) p;
+	}
+	return fn;
+}
+
+// digits needed so that every |word| <= maxabs has a balanced base-256 expansion:
+// L digits cover [-128*(256^L-1)/255, 127*(256^L-1)/255]; L = ring bytes always works (mod 2^W)
+int p1_tc_digits(uint64_t maxabs, int ring_bytes) {
+	unsigned __int128 span = 0;
+	for(int L = 1; L < ring_bytes; L++) {
+		span = span * 256 + 1;                       // (256^L - 1) / 255
+		if((unsigned __int128) maxabs <= 127 * span) return L;
+	}
+	return ring_bytes;
+}
+
 int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, uint64_t *acc_dev) {
-	(void) ctx; (void) data; (void) col_lo; (void) col_hi; (void) owns_target; (void) acc_dev;
-	return p1_fail("tcgen05 Gram kernel not built");
+	tmap_encode_fn encode = get_tmap_encode();
+	P1_CHECK(encode, "p1_local_block: cuTensorMapEncodeTiled is not available from this driver");
+	TcSet gs;
+	gs.col_lo = col_lo;
+	gs.mc = (int) (col_hi - col_lo);
+	gs.m = gs.mc + (owns_target ? 1 : 0);
+	gs.d = data->d;
+	gs.nA = p1_nA(data->d);
+	const int WD = data->bits / 8;
+
+	// digits: from the per-column max |word| the encode pass left in data->stats
+	std::vector<uint64_t> st((data->d + 1) * 4);
+	P1_CUDA(cudaMemcpyAsync(st.data(), data->stats, st.size() * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	uint64_t maxabs = 0;
+	for(int a = 0; a < gs.m; a++) {
+		size_t c = a < gs.mc ? col_lo + a : data->d;
+		if(st[4 * c + 3] > maxabs) maxabs = st[4 * c + 3];
+	}
+	const int L = p1_tc_digits(maxabs, WD);
+	const int G = 2 * L - 1 < WD ? 2 * L - 1 : WD;
+
+	// digit planes P[l][a][row], rows padded to a whole K-block
+	const size_t ldp = p1_round_up(data->ld, TC_BK);
+	const size_t plane_stride = (size_t) gs.m * ldp;
+	const size_t need = plane_stride * L;
+	if(ctx->limb_ws_bytes < need) {
+		if(ctx->limb_ws) {
+			P1_CUDA(cudaStreamSynchronize(ctx->stream));
+			P1_CUDA(cudaFree(ctx->limb_ws));
+			ctx->limb_ws = NULL;
+			ctx->limb_ws_bytes = 0;
+		}
+		P1_CUDA(cudaMalloc(&ctx->limb_ws, need));
+		ctx->limb_ws_bytes = need;
+	}
+	uint8_t *planes = (uint8_t *) ctx->limb_ws;
+	{
+		dim3 grid((unsigned) ((ldp + 1023) / 1024), (unsigned) gs.m);
+		p1_prof_begin(ctx, P1_K_GRAM_LIMBS);
+		if(data->bits == 64) k_limb_split<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, gs, L, planes, ldp, plane_stride);
+		else k_limb_split<uint32_t><<<grid, 256, 0, ctx->stream>>>((const uint32_t *) data->xt, data->ld, gs, L, planes, ldp, plane_stride);
+		P1_LAUNCHED(ctx);
+	}
+
+	// tensor maps over the planes: dims (row, column, limb), u8, 128-byte swizzle
+	CUtensorMap mapA, mapB;
+	cuuint64_t gdim[3] = {(cuuint64_t) ldp, (cuuint64_t) gs.m, (cuuint64_t) L};
+	cuuint64_t gstr[2] = {(cuuint64_t) ldp, (cuuint64_t) plane_stride};
+	cuuint32_t estr[3] = {1, 1, 1};
+	cuuint32_t boxA[3] = {TC_BK, TC_BM, (cuuint32_t) L}, boxB[3] = {TC_BK, TC_BN, (cuuint32_t) L};
+	CUresult r1 = encode(&mapA, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstr, boxA, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+		CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	CUresult r2 = encode(&mapB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstr, boxB, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+		CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	P1_CHECK(r1 == CUDA_SUCCESS && r2 == CUDA_SUCCESS, "p1_local_block: cuTensorMapEncodeTiled failed (%d, %d)", (int) r1, (int) r2);
+
+	TcParams P;
+	P.gs = gs;
+	P.L = L;
+	P.WD = WD;
+	P.G = G;
+	const size_t stage_bytes = (size_t) L * (TC_A_BYTES + TC_B_BYTES);
+	const size_t smem_budget = 220 * 1024;
+	int stages = (int) (smem_budget / stage_bytes);
+	if(stages > 6) stages = 6;
+	P1_CHECK(stages >= 1, "p1_local_block: a pipeline stage of %zu bytes does not fit shared memory", stage_bytes);
+	P.stages = stages;
+	P.tmem_cols = 64;
+	while(P.tmem_cols < (uint32_t) (TC_BN * G)) P.tmem_cols *= 2;
+	P.nblk = (int) ((data->n + TC_BK - 1) / TC_BK);
+	P.chunk_blks = (131071 / L) / TC_BK;             // rows per chunk * L * 2^14 < 2^31
+	if(ctx->opt_tc_chunk_blocks > 0 && ctx->opt_tc_chunk_blocks < P.chunk_blks) P.chunk_blks = (int) ctx->opt_tc_chunk_blocks;
+	// tiles of the lower triangle (incl. the target row as the last row of the set)
+	int tiles = 0;
+	for(int ta = 0; ta * TC_BM < gs.m; ta++) {
+		int lim = TC_BM * (ta + 1) < gs.mc ? TC_BM * (ta + 1) : gs.mc;
+		tiles += (lim + TC_BN - 1) / TC_BN;
+	}
+	int slices = ctx->sm_count / tiles;
+	if(ctx->opt_tc_max_slices > 0 && slices > ctx->opt_tc_max_slices) slices = (int) ctx->opt_tc_max_slices;
+	if(slices < 1) slices = 1;
+	if(slices > P.nblk) slices = P.nblk;
+	P.blk_per_cta = (P.nblk + slices - 1) / slices;
+	slices = (P.nblk + P.blk_per_cta - 1) / P.blk_per_cta;
+	P.acc = acc_dev;
+	const size_t smem = (size_t) stages * stage_bytes + 1024;
+	P1_CUDA(cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	dim3 grid((unsigned) tiles, (unsigned) slices);
+	p1_prof_begin(ctx, P1_K_GRAM_TC);
+	k_gram_tc<<<grid, TC_THREADS, smem, ctx->stream>>>(mapA, mapB, P);
+	P1_LAUNCHED(ctx);
+	return 0;
 }

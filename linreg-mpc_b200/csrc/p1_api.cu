@@ -69,6 +69,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->stage_bytes = 0;
 	ctx->limb_ws = NULL;
 	ctx->limb_ws_bytes = 0;
+	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
 	ctx->prof = false;
 	ctx->prof_open = -1;
 	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
@@ -122,6 +123,16 @@ extern "C" int p1_ctx_wait(p1_ctx *waiter, p1_ctx *signaler) {
 	std::lock_guard<std::mutex> l(waiter->mu);
 	P1_CUDA(cudaSetDevice(waiter->device));
 	P1_CUDA(cudaStreamWaitEvent(waiter->stream, signaler->ev, 0));
+	return 0;
+}
+
+extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
+	P1_ENTER(ctx);
+	P1_CHECK(name && value >= 0, "p1_ctx_set_option: invalid arguments");
+	if(!strcmp(name, "gram_tc_max_slices")) ctx->opt_tc_max_slices = value;
+	else if(!strcmp(name, "gram_tc_chunk_blocks")) ctx->opt_tc_chunk_blocks = value;
+	else if(!strcmp(name, "gram_tc_min_cols")) ctx->opt_tc_min_cols = value;
+	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
 	return 0;
 }
 

@@ -34,6 +34,7 @@ SIGNATURES = {
     "p1_ctx_profile": (c_i, [c_vp, c_i]),
     "p1_ctx_profile_read": (c_i, [c_vp, c_i, ctypes.POINTER(c_d), ctypes.POINTER(c_u64)]),
     "p1_kernel_class_name": (c_cp, [c_i]),
+    "p1_ctx_set_option": (c_i, [c_vp, c_cp, ctypes.c_long]),
     "p1_dev_alloc": (c_i, [c_vp, c_sz, ctypes.POINTER(c_vp)]),
     "p1_dev_free": (c_i, [c_vp, c_vp]),
     "p1_dev_zero": (c_i, [c_vp, c_vp, c_sz]),

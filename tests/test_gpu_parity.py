@@ -143,6 +143,55 @@ def test_local_block_imad_parity(p1lib, oracle, b1, b2, prec, prec2):
     p1lib.p1_ctx_destroy(ctx)
 
 
+def _signed_words(rng, n, d, bits, mag_bits):
+    """ring words that are signed integers of at most mag_bits significant bits (full range if >= bits)"""
+    dt = po.word_dtype(bits)
+    if mag_bits >= bits:
+        return rng.integers(0, 2 ** bits, (n, d), dtype=np.uint64).astype(dt)
+    lim = 2 ** (mag_bits - 1)
+    sdt = np.int64 if bits == 64 else np.int32
+    a = rng.integers(-lim, lim, (n, d)).astype(sdt)
+    a[0, 0], a[1 % n, 0] = lim - 1, -lim       # extremes of the range
+    return a.view(dt)
+
+
+@pytest.mark.parametrize("bits,mag_bits", [(64, 7), (64, 15), (64, 20), (64, 27), (64, 40), (64, 64),
+                                           (32, 6), (32, 14), (32, 22), (32, 32)])
+def test_local_block_tcgen05_digits(p1lib, oracle, bits, mag_bits):
+    """tcgen05 kind::i8 Gram (src/phase1.c:14-20,569-571) for every digit count L = 1..W/8:
+    operands of growing magnitude up to full-range ring words, with the target row."""
+    rng = np.random.default_rng(100 + mag_bits)
+    n, d = 1100, 70
+    Xw = _signed_words(rng, n, d, bits, mag_bits)
+    yw = _signed_words(rng, n, 1, bits, mag_bits)[:, 0].copy()
+    ctx = mkctx(p1lib, bits, bits)
+    data = from_words(p1lib, ctx, Xw, yw)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, bits, 2)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 3, 41, False, bits, 2)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+def test_local_block_tcgen05_shapes(p1lib, oracle, b1, b2, prec, prec2):
+    """several 128x64 output tiles, ragged column/row counts, multi-chunk drains and row
+    slices (forced small through the tuning knobs), on encoded synthetic data"""
+    n, d = 5000, 300
+    X, y, _ = po.generate_lin_regression(n, d, seed=3)
+    nz = oracle.normalizer(prec, n)
+    ctx = mkctx(p1lib, b1, b2)
+    data = encode(p1lib, ctx, X, y, nz, prec)
+    Xw, yw = download(p1lib, ctx, data, n, d, b1)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, b1, 2)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_max_slices", 2))
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_chunk_blocks", 3))   # 20 blocks per CTA -> 7 drains
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, b1, 2)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 100, 229, False, b1, 2)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 171, 300, True, b1, 2)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 @pytest.mark.parametrize("bits", [64, 32])
 def test_diagonal_exact_and_sequential(p1lib, oracle, bits):
     b2 = bits
