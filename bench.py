@@ -209,6 +209,7 @@ def main():
     ap.add_argument("--pipes", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (p1_ctx_set_option), repeatable")
     ap.add_argument("--ot-sample", type=int, default=2, help="inner products of the --use_ot path to time (0 = skip)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -264,6 +265,10 @@ def main():
     batch = args.batch_pairs or max(1, min(64, (256 << 20) // max(1, n_rows * w)))
     box = Phase1Box(lib, n, d, cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
                     row0=row0, n_rows=n_rows, batch_pairs=batch, pipes=args.pipes, gram_algo=gram, group=group)
+    for o in args.opt:
+        name, val = o.split("=")
+        for c in box.ctxs:
+            lib.check(lib.p1_ctx_set_option(c, name.encode(), int(val)))
     key = bytes(range(16))
     seeded = args.aggregation == "masking-seeded"
     macs = box.sched.ring_macs(n, masking=True)

@@ -79,7 +79,8 @@ const char *p1_kernel_class_name(int kernel_class);
  * and multi-slice paths at small sizes, and by bench.py sweeps.
  *   "gram_tc_max_slices"   : upper bound on the row slices (grid.y) of k_gram_tc
  *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
- *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on */
+ *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on
+ *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM) */
 int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
 
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);

@@ -24,7 +24,7 @@ struct p1_cot {
 	size_t n_rows;
 };
 
-#define COT_GROUPS 4
+#define COT_GROUPS 8
 #define COT_THREADS (128 * COT_GROUPS)
 
 struct CotParams {
@@ -49,28 +49,30 @@ __device__ __forceinline__ void group_sync(int g) {
 
 // ROLE 0: receiver extend, ROLE 1: sender step
 template <typename W, int ROLE>
-__global__ void __launch_bounds__(COT_THREADS) k_cot_tiles(const CotParams P) {
-	extern __shared__ __align__(16) uint32_t smem[];
+__global__ void __launch_bounds__(COT_THREADS, 1) k_cot_tiles(const CotParams P) {
+	extern __shared__ __align__(256) uint8_t smem[];
 	constexpr int NK = ROLE == 0 ? 2 : 1;
 	constexpr int WB = sizeof(W) * 8;
-	uint32_t *sT = smem;                       // 256 x 32 replicated T0
-	uint32_t *sK = sT + 256 * 32;              // NK x 44 x 128
-	uint32_t *sR = sK + NK * 44 * 128;         // COT_GROUPS x 128 x 5
-	aes_load_tables<32, 1>(sT, P.T0);
+	// [key schedules NK x 44 x 128 | gap | AES tables (64 KB aligned) | transpose rows COT_GROUPS x 128 x 5]
+	uint32_t *sK = reinterpret_cast<uint32_t *>(smem);
+	uint8_t *sT = smem + aes_table_offset(smem, NK * 44 * 128 * 4, COT_GROUPS * 128 * 5 * 4);
+	uint32_t *sR = reinterpret_cast<uint32_t *>(sT + AES_TAB_BYTES);
+	aes_load_tables(sT, P.T0);
 	for(int i = threadIdx.x; i < NK * 44 * 128; i += blockDim.x) sK[i] = P.keys[i];
 	__syncthreads();
 	const int g = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5, lane = t & 31;
+	const uint32_t lb = aes_lane_base(sT, (uint32_t) lane);
 	uint32_t *myR = sR + g * 128 * 5;
 	const bool dbit = ROLE == 1 && ((P.delta[t >> 5] >> (t & 31)) & 1);
 	uint64_t dot = 0;
 	for(uint64_t tile = (uint64_t) blockIdx.x * COT_GROUPS + g; tile < P.tiles; tile += (uint64_t) gridDim.x * COT_GROUPS) {
 		// ---- column phase: thread t = column t of the kappa x m matrix
 		uint32_t a[4];
-		aes_ctr_block_k<32, 1>(AesSmemKey(sK, 128, t), sT, lane, P.ctr0 + tile, a);
+		aes_ctr_block_k(AesSmemKey(sK, 128, t), lb, P.ctr0 + tile, a);
 		uint4 *up = reinterpret_cast<uint4 *>((char *) P.u + tile * 2048) + t;
 		if(ROLE == 0) {
 			uint32_t b[4];
-			aes_ctr_block_k<32, 1>(AesSmemKey(sK + 44 * 128, 128, t), sT, lane, P.ctr0 + tile, b);
+			aes_ctr_block_k(AesSmemKey(sK + 44 * 128, 128, t), lb, P.ctr0 + tile, b);
 			const uint4 ch = *(reinterpret_cast<const uint4 *>(P.col) + tile); // 128 choice bits = 16 bytes of the column
 			*up = make_uint4(a[0] ^ b[0] ^ ch.x, a[1] ^ b[1] ^ ch.y, a[2] ^ b[2] ^ ch.z, a[3] ^ b[3] ^ ch.w);
 		} else if(dbit) {
@@ -99,13 +101,13 @@ __global__ void __launch_bounds__(COT_THREADS) k_cot_tiles(const CotParams P) {
 		x0 ^= (uint32_t) J;
 		x1 ^= (uint32_t) (J >> 32);
 		uint32_t h[4];
-		aes_encrypt<32, 1>(AesConstKey(P.hash), sT, lane, x0, x1, x2, x3, h);
+		aes_encrypt(AesConstKey(P.hash), lb, x0, x1, x2, x3, h);
 		W pad0 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ x1)) << 32) | (h[0] ^ x0)) : (W) (h[0] ^ x0);
 		if(ROLE == 0) {
 			reinterpret_cast<W *>(P.pads)[tile * 128 + t] = pad0;
 		} else {
 			uint32_t y0 = x0 ^ P.delta[0], y1 = x1 ^ P.delta[1], y2 = x2 ^ P.delta[2], y3 = x3 ^ P.delta[3];
-			aes_encrypt<32, 1>(AesConstKey(P.hash), sT, lane, y0, y1, y2, y3, h);
+			aes_encrypt(AesConstKey(P.hash), lb, y0, y1, y2, y3, h);
 			W pad1 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ y1)) << 32) | (h[0] ^ y0)) : (W) (h[0] ^ y0);
 			const uint64_t ni = tile * 128 + t, k = ni / WB;
 			const int bit = (int) (ni % WB);
@@ -261,7 +263,8 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 		s->n_rows = data->n;
 	}
 	constexpr int NK = ROLE == 0 ? 2 : 1;
-	size_t smem = (256 * 32 + NK * 44 * 128 + COT_GROUPS * 128 * 5) * sizeof(uint32_t);
+	size_t smem = AES_SMEM_BYTES + COT_GROUPS * 128 * 5 * sizeof(uint32_t);  // key schedules live in the gap below the tables
+	static_assert(2 * 44 * 128 * 4 <= AES_SMEM_GAP, "key schedules must fit below the AES tables");
 	uint64_t grid = (P.tiles + COT_GROUPS - 1) / COT_GROUPS;
 	int per_sm = 0;
 	if(s->bits == 64) {

@@ -72,6 +72,22 @@ const uint32_t *aes_host_T0(void) {
 	return h_T0;
 }
 
+static inline uint32_t rotl8(uint32_t v, int k) { return k ? (v << (8 * k)) | (v >> (32 - 8 * k)) : v; }
+static inline uint32_t bswap32(uint32_t v) { return (v >> 24) | ((v >> 8) & 0xff00u) | ((v << 8) & 0xff0000u) | (v << 24); }
+
+// round 1 of the counter block 0^64 || BE32(hi) || BE32(lo) without the lookups of the
+// low counter word: T_k[x] = rotl(T0[x], 8k)
+void aes_host_ctr_key(const uint8_t key[16], uint32_t hi, AesCtrKey *out) {
+	aes_host_expand(key, &out->k);
+	const uint32_t *rk = out->k.rk;
+	const uint32_t s0 = rk[0], s1 = rk[1], s2 = bswap32(hi) ^ rk[2];
+	out->hi = hi;
+	out->c1[0] = h_T0[s0 & 0xff] ^ rotl8(h_T0[(s1 >> 8) & 0xff], 1) ^ rotl8(h_T0[(s2 >> 16) & 0xff], 2) ^ rk[4];
+	out->c1[1] = h_T0[s1 & 0xff] ^ rotl8(h_T0[(s2 >> 8) & 0xff], 1) ^ rotl8(h_T0[s0 >> 24], 3) ^ rk[5];
+	out->c1[2] = h_T0[s2 & 0xff] ^ rotl8(h_T0[(s0 >> 16) & 0xff], 2) ^ rotl8(h_T0[s1 >> 24], 3) ^ rk[6];
+	out->c1[3] = rotl8(h_T0[(s0 >> 8) & 0xff], 1) ^ rotl8(h_T0[(s1 >> 16) & 0xff], 2) ^ rotl8(h_T0[s2 >> 24], 3) ^ rk[7];
+}
+
 static uint32_t *d_T0[64] = {NULL};
 
 int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
@@ -92,8 +108,11 @@ int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
 
 #define TI_U 4 // stream blocks per lane per work unit
 
+#define TI_THREADS 1024         // register cap (launch bound); the launch uses TI_THREADS_DEFAULT
+#define TI_THREADS_DEFAULT 768  // leaves registers and thread slots on every SM for the HBM-bound party kernels of the other pipe
+
 struct TiParams {
-	AesKey key;
+	AesCtrKey key;
 	uint64_t q0;
 	uint32_t count;
 	uint64_t n_total, row0, n_rows;
@@ -104,24 +123,25 @@ struct TiParams {
 	const uint32_t *T0;
 };
 
-template <typename W, int REPL, int NTAB, bool ALIGNED>
-__global__ void __launch_bounds__(512) k_ti_generate(const TiParams P) {
-	extern __shared__ __align__(16) uint32_t sT[];
+template <typename W, bool ALIGNED>
+__global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P) {
+	extern __shared__ __align__(256) uint8_t smem[];
 	constexpr int w = sizeof(W);
 	constexpr int EPB = 16 / w; // elements per AES block
-	aes_load_tables<REPL, NTAB>(sT, P.T0);
+	uint8_t *sT = smem + aes_table_offset(smem, 0, 0);
+	aes_load_tables(sT, P.T0);
 	__syncthreads();
-	const uint32_t lane = threadIdx.x & 31, lane_off = lane & (REPL - 1);
-	const uint64_t warps_total = (uint64_t) gridDim.x * (blockDim.x >> 5);
-	const uint64_t gw = (uint64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	const uint64_t units = (uint64_t) P.count * P.units_per_pair;
+	const uint32_t lane = threadIdx.x & 31, lb = aes_lane_base(sT, lane);
+	const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
+	const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const uint32_t units = P.count * P.units_per_pair;   // < 2^32, checked by the launcher
 	const bool need_x = P.x || P.xy, need_y = P.y || P.xy;
 	const uint64_t nbytes = P.n_rows * w;        // bytes of one mask on this shard
 	const uint64_t ydelta = P.n_total * w;       // stream distance x -> y
 	const uint32_t ysh = (uint32_t) (ydelta & 15);
 
-	for(uint64_t u = gw; u < units; u += warps_total) {
-		const uint32_t p = (uint32_t) (u / P.units_per_pair), uu = (uint32_t) (u % P.units_per_pair);
+	for(uint32_t u = gw; u < units; u += warps_total) {
+		const uint32_t p = u / P.units_per_pair, uu = u - p * P.units_per_pair;
 		const uint64_t W0 = (P.q0 + p) * (2 * P.n_total + 1);
 		const uint64_t X0 = (W0 + P.row0) * w;       // stream byte of this shard's x[0]
 		const uint64_t b_first = X0 >> 4;
@@ -134,16 +154,16 @@ __global__ void __launch_bounds__(512) k_ti_generate(const TiParams P) {
 			const int64_t o = (int64_t) (B << 4) - (int64_t) X0; // byte offset of this block in the shard's mask
 			if(o >= (int64_t) nbytes) continue;                  // past the end (o > -16 always)
 			uint32_t xs[4] = {0, 0, 0, 0}, ys[4] = {0, 0, 0, 0};
-			if(need_x) aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, B, xs);
+			if(need_x) aes_ctr_block(P.key, lb, B, xs);
 			if(need_y) {
 				const uint64_t By = ((B << 4) + ydelta) >> 4;
 				if(ALIGNED) {
-					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By, ys);
+					aes_ctr_block(P.key, lb, By, ys);
 				} else {
 					// y bytes for these positions straddle two stream blocks
 					uint32_t ya[4], yb[4];
-					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By, ya);
-					aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, By + 1, yb);
+					aes_ctr_block(P.key, lb, By, ya);
+					aes_ctr_block(P.key, lb, By + 1, yb);
 					const uint32_t ws = ysh >> 2; // whole 32-bit words (ysh is a multiple of w >= 4)
 #pragma unroll
 					for(int c = 0; c < 4; c++) {
@@ -181,7 +201,7 @@ __global__ void __launch_bounds__(512) k_ti_generate(const TiParams P) {
 			// r = S[W0 + 2 n_total] (src/phase1.c:273)
 			const uint64_t Rb = (W0 + 2 * P.n_total) * w;
 			uint32_t rs[4];
-			aes_ctr_block<REPL, NTAB>(P.key, sT, lane_off, Rb >> 4, rs);
+			aes_ctr_block(P.key, lb, Rb >> 4, rs);
 			const uint32_t wi = (uint32_t) (Rb & 15) >> 2;
 			uint32_t lo = 0, hi = 0;
 #pragma unroll
@@ -194,30 +214,24 @@ __global__ void __launch_bounds__(512) k_ti_generate(const TiParams P) {
 	}
 }
 
-template <typename W, int REPL, int NTAB>
+template <typename W>
 static int launch_ti(p1_ctx *ctx, const TiParams &P, bool aligned) {
-	size_t smem = (size_t) NTAB * 256 * REPL * sizeof(uint32_t);
-	int blocks_per_sm = 0;
-	if(aligned) {
-		P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, REPL, NTAB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_ti_generate<W, REPL, NTAB, true>, 512, smem));
-	} else {
-		P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, REPL, NTAB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-		P1_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_ti_generate<W, REPL, NTAB, false>, 512, smem));
-	}
-	P1_CHECK(blocks_per_sm > 0, "k_ti_generate does not fit on an SM");
+	const size_t smem = AES_SMEM_BYTES;
+	if(aligned) P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	else P1_CUDA(cudaFuncSetAttribute(k_ti_generate<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	// persistent: one 1024-thread CTA per SM (the 128 KB table allows no more)
 	uint64_t units = (uint64_t) P.count * P.units_per_pair;
-	uint64_t grid = (uint64_t) ctx->sm_count * blocks_per_sm;
-	uint64_t need = (units + 15) / 16; // 16 warps per CTA
+	P1_CHECK(units < 0xffffffffull, "p1_ti_generate: batch too large (%llu work units)", (unsigned long long) units);
+	const unsigned threads = ctx->opt_ti_threads ? (unsigned) ctx->opt_ti_threads : TI_THREADS_DEFAULT;
+	uint64_t grid = (uint64_t) ctx->sm_count;
+	uint64_t need = (units + threads / 32 - 1) / (threads / 32);
 	if(grid > need) grid = need;
 	p1_prof_begin(ctx, P1_K_TI);
-	if(aligned) k_ti_generate<W, REPL, NTAB, true><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
-	else k_ti_generate<W, REPL, NTAB, false><<<(unsigned) grid, 512, smem, ctx->stream>>>(P);
+	if(aligned) k_ti_generate<W, true><<<(unsigned) grid, threads, smem, ctx->stream>>>(P);
+	else k_ti_generate<W, false><<<(unsigned) grid, threads, smem, ctx->stream>>>(P);
 	P1_LAUNCHED(ctx);
 	return 0;
 }
-
-static int g_variant = -1; // 0: T0 x32 + PRMT rotations, 1: four stored tables x32
 
 extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count,
 	size_t n_total, size_t row0, size_t n_rows, void *x_dev, void *y_dev, size_t ld_words,
@@ -230,14 +244,11 @@ extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, s
 	P1_CHECK(n_rows > 0 && row0 + n_rows <= n_total, "p1_ti_generate: rows [%zu,%zu) outside [0,%zu)", row0, row0 + n_rows, n_total);
 	P1_CHECK((!x_dev && !y_dev) || ld_words >= n_rows, "p1_ti_generate: ld_words %zu < n_rows %zu", ld_words, n_rows);
 	P1_CHECK(count <= 0xffffffffu, "p1_ti_generate: batch too large");
-	if(g_variant < 0) {
-		const char *e = getenv("P1_AES_VARIANT");
-		g_variant = e ? atoi(e) : 0;
-	}
 	const int w = ctx->bits_p1 / 8;
 	TiParams P;
 	if(aes_device_T0(ctx, &P.T0)) return 1;
-	aes_host_expand(key, &P.key);
+	// most of a launch shares the high counter word of its first stream block
+	aes_host_ctr_key(key, (uint32_t) ((((uint64_t) q0 * (2 * (uint64_t) n_total + 1) + row0) * w) >> 36), &P.key);
 	P.q0 = q0;
 	P.count = (uint32_t) count;
 	P.n_total = n_total;
@@ -253,10 +264,6 @@ extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, s
 	P.units_per_pair = (uint32_t) ((nblk + 32 * TI_U - 1) / (32 * TI_U));
 	if(xy_dev) P1_CUDA(cudaMemsetAsync(xy_dev, 0, count * sizeof(uint64_t), ctx->stream));
 	bool aligned = ((uint64_t) n_total * w) % 16 == 0;
-	if(w == 8) {
-		if(g_variant == 1) return launch_ti<uint64_t, 32, 4>(ctx, P, aligned);
-		return launch_ti<uint64_t, 32, 1>(ctx, P, aligned);
-	}
-	if(g_variant == 1) return launch_ti<uint32_t, 32, 4>(ctx, P, aligned);
-	return launch_ti<uint32_t, 32, 1>(ctx, P, aligned);
+	if(w == 8) return launch_ti<uint64_t>(ctx, P, aligned);
+	return launch_ti<uint32_t>(ctx, P, aligned);
 }

@@ -70,6 +70,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->limb_ws = NULL;
 	ctx->limb_ws_bytes = 0;
 	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
+	ctx->opt_ti_threads = 0;
 	ctx->prof = false;
 	ctx->prof_open = -1;
 	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
@@ -132,6 +133,10 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 	if(!strcmp(name, "gram_tc_max_slices")) ctx->opt_tc_max_slices = value;
 	else if(!strcmp(name, "gram_tc_chunk_blocks")) ctx->opt_tc_chunk_blocks = value;
 	else if(!strcmp(name, "gram_tc_min_cols")) ctx->opt_tc_min_cols = value;
+	else if(!strcmp(name, "ti_threads")) {
+		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 1024), "ti_threads must be a multiple of 32 in [32,1024]");
+		ctx->opt_ti_threads = value;
+	}
 	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
 	return 0;
 }

@@ -27,6 +27,7 @@ struct p1_ctx {
 	// tcgen05 Gram workspace (limb planes), grown on demand
 	void *limb_ws;  size_t limb_ws_bytes;
 	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols;
+	long opt_ti_threads;              // threads per CTA of k_ti_generate (0 = default)
 	// per-kernel-class event timing (p1_ctx_profile)
 	bool prof;
 	int prof_open;                       // class of the launch being bracketed, -1 if none
