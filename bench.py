@@ -334,9 +334,21 @@ def main():
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
+    # no int8 entry in MEASURED_PEAKS.json: dense int8 = 2x dense bf16 on this part, so 2x the measured bf16 burst
+    int8_peak = 2.0 * float(peaks.get("bf16_tflops", 1590.0))
+    int8_nominal = 4500.0
     C = box.sched.num_cross
     nb = n_rows * w
-    Lpairs = int(np.count_nonzero(box.sched.kind == 1))
+    local_macs, tc_ops, limb_bytes = 0, 0, 0
+    for k in range(box.sched.num_dp):
+        lo, hi = box.sched.col_range(k)
+        m = hi - lo + int(k == box.sched.num_dp - 1)
+        pairs = m * (m - 1) // 2
+        Lk = ctypes.c_int(0)
+        lib.check(lib.p1_gram_digits(box.ctxs[0], box.data, lo, hi, int(k == box.sched.num_dp - 1), ctypes.byref(Lk)))
+        local_macs += n_rows * pairs
+        tc_ops += 2 * Lk.value ** 2 * n_rows * pairs         # int8 ops of the lower-triangle pairs (executed digits)
+        limb_bytes += m * n_rows * (w + Lk.value)
     alg_bytes = {  # per step on this rank
         "encode": (8 + w) * (n_rows * d + n_rows),
         "ti_generate": C * (2 * nb) * (1 if not seeded else 2),     # keystream words written
@@ -344,7 +356,7 @@ def main():
         "party_a_step": C * 4 * nb,                                  # column, mask, peer message read; message written
         "party_b_share": C * 2 * nb,                                 # peer message + column read
         "gram_imad": (d + 1) * nb,                                   # every owned column read once
-        "gram_limbs": 0, "gram_tc": 0,
+        "gram_limbs": limb_bytes,                                    # words read, digit planes written
     }
     kernels = {}
     for name, pr in prof.items():
@@ -352,15 +364,32 @@ def main():
         if alg_bytes.get(name):
             gbs = alg_bytes[name] / (pr["ms_per_step"] * 1e-3) / 1e9
             ent.update(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak)
+        if name == "gram_tc" and tc_ops:
+            tops = tc_ops / (pr["ms_per_step"] * 1e-3) / 1e12
+            ent.update(bound="tensor", achieved=tops, peak=int8_peak, unit="TOP/s (int8)", frac=tops / int8_peak,
+                       frac_of_nominal_dense_int8=tops / int8_nominal, ring_gmacs=local_macs / (pr["ms_per_step"] * 1e-3) / 1e9,
+                       peak_source="2 x measured dense bf16 burst (no int8 entry in MEASURED_PEAKS.json); nominal dense int8 is 4500")
+        if name == "ti_generate":
+            # the honest bound of the T-table AES: 16 lookups x 10 rounds - 12 folded = 148 shared-memory
+            # lookups per 16-byte block, one 32-lane LDS per clock per SM
+            blocks = C * (2 * nb + 16) / 16.0 * (1 if not seeded else 2)
+            sm_clk = (clocks or {}).get("sm_mhz") or 1965.0
+            lsu_peak = 148 * 32 * sm_clk * 1e6 / 148.0          # blocks/s at one LDS per clock per SM
+            ent.update(lsu_bound={"achieved_blocks_per_s": blocks / (pr["ms_per_step"] * 1e-3), "peak_blocks_per_s": lsu_peak,
+                                  "frac": blocks / (pr["ms_per_step"] * 1e-3) / lsu_peak,
+                                  "note": "148 LDS per AES block, 128 B/clk/SM shared-memory port, at the sampled SM clock"})
         kernels[name] = ent
     dominant = max(prof, key=lambda k: prof[k]["ms_per_step"]) if prof else None
     roofline = None
     if dominant and "achieved" in kernels[dominant]:
         kd = kernels[dominant]
-        roofline = {"kernel": dominant, "bound": "hbm", "achieved": kd["achieved"], "peak": hbm_peak, "unit": "GB/s",
-                    "frac": kd["frac"], "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": alg_bytes[dominant] / max(kd["launches_per_step"], 1),
+        roofline = {"kernel": dominant, "bound": kd["bound"], "achieved": kd["achieved"], "peak": kd["peak"], "unit": kd["unit"],
+                    "frac": kd["frac"], "traffic": None, "peak_source": kd.get("peak_source", peak_src),
                     "avg_launch_ms": kd["avg_ms"]}
+        if kd["bound"] == "hbm":
+            roofline["algorithmic_bytes_per_launch"] = alg_bytes[dominant] / max(kd["launches_per_step"], 1)
+        if "lsu_bound" in kd:
+            roofline["lsu_bound"] = kd["lsu_bound"]
 
     # ---- end to end: host buffers in, shares out
     e2e = None

@@ -139,6 +139,11 @@ size_t p1_acc_len(size_t d);
 int p1_local_block(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target,
                    uint64_t *acc_dev, int algo);
 
+/* Number of balanced base-256 digits per word the tcgen05 path uses for this block (from
+ * the max |word| statistics of the encode pass): the kernel executes 2*L*L int8 ops per
+ * ring MAC.  Reporting aid for rooflines; synchronises the stream. */
+int p1_gram_digits(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, int *digits);
+
 /* Sequential double-precision diagonal, the literal loop of src/phase1.c:563-566:
  *     for k: xy += pow(fixed_to_double_p1(word_k, precision), 2) * pow(2, precision)
  * continued from xy_inout[c] over this shard's rows for columns col_lo..col_hi-1

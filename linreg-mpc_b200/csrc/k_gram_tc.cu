@@ -14,10 +14,12 @@
 // |.| <= 2^14, so after at most floor((2^17-1)/L) rows the accumulators are drained
 // into 64-bit registers (sum_s acc_s << 8s), which keeps every s32 sum exact.
 //
-// Data path.  k_limb_split writes digit planes P[l][col][row] (K-major: the contraction
-// index k = row is contiguous).  One CTA owns a 128 x 64 block of the (column x column)
-// output and a slice of the rows:
-//   warp 0    TMA producer: box (128 rows, 128|64 cols, L limbs) -> smem, SWIZZLE_128B
+// Data path.  k_limb_split writes digit planes P[kblock][l][col][128 rows] (K-major: the
+// contraction index k = row is contiguous inside a 128-row block, and everything one
+// pipeline stage needs is one contiguous region per limb - a stage touches one or two
+// 2 MB pages instead of one page per column, which is what the per-SM TMA rate needs).
+// One CTA owns a 128 x 64 block of the (column x column) output and a slice of the rows:
+//   warp 0    TMA producer: box (128 rows, 128|64 cols, L limbs, 1 block) -> smem, SWIZZLE_128B
 //   warp 1    MMA issuer:   for each K-step of 32 rows and each A-limb l one
 //             tcgen05.mma  D[:, 64l .. 64(l+c)) += A_l (128 x 32) * [B_0;..;B_{c-1}]^T
 //             (the B limb tiles are stacked in smem, so N = 64c covers c shift groups)
@@ -49,10 +51,11 @@ __device__ __forceinline__ size_t tc_slot(const TcSet &gs, int a, int b) {
 
 // ------------------------------------------------------------------ digit planes
 
-// grid (ceil(ldp/1024), m), block 256: thread = 4 consecutive rows of one column
+// grid (ceil(ldp/1024), m), block 256: thread = 4 consecutive rows of one column; a warp
+// writes one whole 128-byte row of P[kblock][l][col][.] per limb
 template <typename W>
 __global__ void __launch_bounds__(256) k_limb_split(const W *__restrict__ xt, size_t ld, TcSet gs, int L,
-	uint8_t *__restrict__ planes, size_t ldp, size_t plane_stride) {
+	uint8_t *__restrict__ planes, size_t ldp) {
 	typedef typename p1_word<W>::s S;
 	size_t r = ((size_t) blockIdx.x * 256 + threadIdx.x) * 4;
 	if(r >= ldp) return;
@@ -71,7 +74,8 @@ __global__ void __launch_bounds__(256) k_limb_split(const W *__restrict__ xt, si
 	} else {
 		v[0] = v[1] = v[2] = v[3] = 0;
 	}
-	uint8_t *dst = planes + (size_t) a * ldp + r;
+	const size_t kb = r / TC_BK, rr = r % TC_BK;
+	uint8_t *dst = planes + ((kb * L) * (size_t) gs.m + a) * TC_BK + rr;
 	for(int l = 0; l < L; l++) {
 		uint32_t packed = 0;
 #pragma unroll
@@ -80,7 +84,7 @@ __global__ void __launch_bounds__(256) k_limb_split(const W *__restrict__ xt, si
 			v[u] = (v[u] - dg) >> 8;
 			packed |= ((uint32_t) dg & 0xffu) << (8 * u);
 		}
-		*reinterpret_cast<uint32_t *>(dst + (size_t) l * plane_stride) = packed;
+		*reinterpret_cast<uint32_t *>(dst + (size_t) l * gs.m * TC_BK) = packed;
 	}
 }
 
@@ -109,10 +113,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 		"DONE_%=:\n\t"
 		"}" ::"r"(addr), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2) {
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2, int c3) {
 	asm volatile(
-		"cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-		::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+		"cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+		::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
 		: "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -126,8 +130,8 @@ __device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t a_desc, uint
 		"{\n\t"
 		".reg .pred p;\n\t"
 		"setp.ne.b32 p, %4, 0;\n\t"
-		"tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t"
-		"}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u), "r"(0u), "r"(0u), "r"(0u)
+		"tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
+		"}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
 		: "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t (&v)[32]) {
@@ -164,9 +168,6 @@ __device__ __forceinline__ uint32_t tc_idesc(int N) {
 
 struct TcParams {
 	TcSet gs;
-	int L;                 // digits per word
-	int WD;                // ring bytes (8 or 4): pairs with l+m >= WD vanish mod 2^W
-	int G;                 // shift groups = min(2L-1, WD)
 	int stages;
 	uint32_t tmem_cols;    // power of two >= 64*G
 	int nblk;              // K-blocks (of TC_BK rows) in the shard
@@ -175,15 +176,26 @@ struct TcParams {
 	uint64_t *acc;
 };
 
+// high word of the K-major SWIZZLE_128B descriptor (SBO = 1024 B, version 1, swizzle mode 2);
+// the low word is (addr >> 4) | LBO << 16, so advancing the operand by n bytes adds n >> 4
+#define TC_DESC_HI (64u | (1u << 14) | (2u << 29))
+__device__ __forceinline__ uint64_t tc_desc(uint32_t lo) { return ((uint64_t) TC_DESC_HI << 32) | lo; }
+
+// L = digits per word, WD = ring bytes (8 or 4): pairs with l+m >= WD vanish mod 2^W.
+// Everything the single MMA-issuing thread needs is a compile-time constant: the issue
+// loop is two integer adds per tcgen05.mma (measured: with run-time L the issue thread
+// itself was the bottleneck at ~200 clk per MMA).
+template <int L, int WD>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant__ CUtensorMap mapA,
 	const __grid_constant__ CUtensorMap mapB, const TcParams P) {
+	constexpr int G = 2 * L - 1 < WD ? 2 * L - 1 : WD;          // shift groups
+	constexpr uint32_t STAGE_BYTES = (uint32_t) L * (TC_A_BYTES + TC_B_BYTES);
 	extern __shared__ __align__(1024) uint8_t smem_raw[];
 	__shared__ __align__(8) uint64_t bar_full[8], bar_empty[8], bar_tfull, bar_tempty;
 	__shared__ uint32_t tmem_base_s;
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const int L = P.L, G = P.G, S = P.stages;
-	const uint32_t stage_bytes = (uint32_t) L * (TC_A_BYTES + TC_B_BYTES);
+	const int S = P.stages;
 	uint8_t *smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
 
 	// tile decode: ta = 128-wide row tile, tb = 64-wide column tile with 64*tb < min(128*(ta+1), mc)
@@ -222,49 +234,54 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 	if(warp == 0) {
 		// ===== TMA producer
 		if(lane == 0) {
+			int s = 0;
+			uint32_t ph = 0;
 			for(int b = 0; b < nb; b++) {
-				int s = b % S;
-				uint32_t ph = (uint32_t) (b / S) & 1u;
 				mbar_wait(&bar_empty[s], ph ^ 1u);
-				mbar_expect_tx(&bar_full[s], stage_bytes);
-				uint8_t *sa = smem + (size_t) s * stage_bytes, *sb = sa + (size_t) L * TC_A_BYTES;
-				int k0 = (blk_lo + b) * TC_BK;
-				tma_load_3d(sa, &mapA, &bar_full[s], k0, ta * TC_BM, 0);
-				tma_load_3d(sb, &mapB, &bar_full[s], k0, tb * TC_BN, 0);
+				mbar_expect_tx(&bar_full[s], STAGE_BYTES);
+				uint8_t *sa = smem + (size_t) s * STAGE_BYTES, *sb = sa + (size_t) L * TC_A_BYTES;
+				tma_load_4d(sa, &mapA, &bar_full[s], 0, ta * TC_BM, 0, blk_lo + b);
+				tma_load_4d(sb, &mapB, &bar_full[s], 0, tb * TC_BN, 0, blk_lo + b);
+				if(++s == S) { s = 0; ph ^= 1u; }
 			}
 		}
 	} else if(warp == 1) {
 		// ===== MMA issuer (one thread)
 		if(lane == 0) {
-			uint32_t chunk = 0;
+			const uint32_t lo0 = ((smem_u32(smem) >> 4) & 0x3fffu) | (1u << 16);
+			int s = 0, in_chunk = 0;
+			uint32_t ph = 0, chunk = 0;
 			for(int b = 0; b < nb; b++) {
-				if(b % P.chunk_blks == 0) {
+				if(in_chunk == 0) {
 					// the epilogue has drained and zeroed the accumulators of the previous chunk
 					mbar_wait(&bar_tempty, chunk & 1u);
 					tc_fence_after();
 				}
-				int s = b % S;
-				uint32_t ph = (uint32_t) (b / S) & 1u;
 				mbar_wait(&bar_full[s], ph);
 				tc_fence_after();
-				uint32_t sa = smem_u32(smem + (size_t) s * stage_bytes), sb = sa + (uint32_t) L * TC_A_BYTES;
+				const uint32_t a_lo = lo0 + (uint32_t) s * (STAGE_BYTES >> 4), b_lo = a_lo + (uint32_t) L * (TC_A_BYTES >> 4);
+				// limb-major order: the four K-steps of one A limb accumulate into the same TMEM columns
 #pragma unroll
-				for(int k4 = 0; k4 < TC_BK / 32; k4++) {
-					for(int l = 0; l < L; l++) {
-						int cnt = L < P.WD - l ? L : P.WD - l;     // B limbs m with l+m < WD
-						if(cnt <= 0) break;
-						uint64_t da = tc_smem_desc(sa + (uint32_t) l * TC_A_BYTES + (uint32_t) k4 * 32);
-						int c0 = cnt < 4 ? cnt : 4;
-						tc_mma_i8(tmem + (uint32_t) (TC_BN * l), da, tc_smem_desc(sb + (uint32_t) k4 * 32), tc_idesc(TC_BN * c0), 1u);
-						if(cnt > 4)
-							tc_mma_i8(tmem + (uint32_t) (TC_BN * (l + 4)), da, tc_smem_desc(sb + 4u * TC_B_BYTES + (uint32_t) k4 * 32),
-								tc_idesc(TC_BN * (cnt - 4)), 1u);
+				for(int l = 0; l < L; l++) {
+					const int cnt = L < WD - l ? L : WD - l;      // B limbs m with l+m < WD (compile-time after unrolling)
+					if(cnt > 0) {
+						const int c0 = cnt < 4 ? cnt : 4;
+#pragma unroll
+						for(int k4 = 0; k4 < TC_BK / 32; k4++) {
+							const uint64_t da = tc_desc(a_lo + (uint32_t) (l * (TC_A_BYTES >> 4) + k4 * 2));
+							tc_mma_i8(tmem + (uint32_t) (TC_BN * l), da, tc_desc(b_lo + (uint32_t) (k4 * 2)), tc_idesc(TC_BN * c0), 1u);
+							if(cnt > 4)
+								tc_mma_i8(tmem + (uint32_t) (TC_BN * (l + 4)), da, tc_desc(b_lo + (uint32_t) (4 * (TC_B_BYTES >> 4) + k4 * 2)),
+									tc_idesc(TC_BN * (cnt - 4)), 1u);
+						}
 					}
 				}
 				tc_commit(&bar_empty[s]);          // frees the smem stage once these MMAs have read it
-				if((b + 1) % P.chunk_blks == 0 || b + 1 == nb) {
+				if(++s == S) { s = 0; ph ^= 1u; }
+				if(++in_chunk == P.chunk_blks || b + 1 == nb) {
 					tc_commit(&bar_tfull);         // accumulators of this chunk are complete
 					chunk++;
+					in_chunk = 0;
 				}
 			}
 		}
@@ -275,6 +292,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 		uint64_t out[TC_BN];
 #pragma unroll
 		for(int c = 0; c < TC_BN; c++) out[c] = 0;
+#pragma unroll
 		for(int g = 0; g < 2 * G; g++) tmem_zero32(tlane + (uint32_t) (32 * g));
 		tmem_wait_st();
 		tc_fence_before();
@@ -284,18 +302,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 			mbar_wait(&bar_tfull, (uint32_t) ch & 1u);
 			tc_fence_after();
 #pragma unroll
-			for(int s = 0; s < 8; s++) {
-				if(s < G) {
+			for(int s = 0; s < G; s++) {
 #pragma unroll
-					for(int h = 0; h < 2; h++) {
-						uint32_t v[32];
-						tmem_ld32(tlane + (uint32_t) (TC_BN * s + 32 * h), v);
+				for(int h = 0; h < 2; h++) {
+					uint32_t v[32];
+					tmem_ld32(tlane + (uint32_t) (TC_BN * s + 32 * h), v);
 #pragma unroll
-						for(int c = 0; c < 32; c++) out[32 * h + c] += (uint64_t) (int64_t) (int32_t) v[c] << (8 * s);
-					}
+					for(int c = 0; c < 32; c++) out[32 * h + c] += (uint64_t) (int64_t) (int32_t) v[c] << (8 * s);
 				}
 			}
 			if(ch + 1 < nchunks) {
+#pragma unroll
 				for(int g = 0; g < 2 * G; g++) tmem_zero32(tlane + (uint32_t) (32 * g));
 				tmem_wait_st();
 				tc_fence_before();
@@ -318,6 +335,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 		tc_fence_after();
 		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(P.tmem_cols) : "memory");
 	}
+}
+
+typedef void (*tc_kernel_t)(const CUtensorMap, const CUtensorMap, const TcParams);
+template <int WD> static tc_kernel_t tc_kernel_for(int L) {
+	switch(L) {
+	case 1: return k_gram_tc<1, WD>;
+	case 2: return k_gram_tc<2, WD>;
+	case 3: return k_gram_tc<3, WD>;
+	case 4: return k_gram_tc<4, WD>;
+	case 5: return WD == 8 ? k_gram_tc<5, 8> : NULL;
+	case 6: return WD == 8 ? k_gram_tc<6, 8> : NULL;
+	case 7: return WD == 8 ? k_gram_tc<7, 8> : NULL;
+	case 8: return WD == 8 ? k_gram_tc<8, 8> : NULL;
+	}
+	return NULL;
 }
 
 // ------------------------------------------------------------------ host side
@@ -347,6 +379,26 @@ int p1_tc_digits(uint64_t maxabs, int ring_bytes) {
 	return ring_bytes;
 }
 
+// digits for the block [col_lo, col_hi) (+ target): from the per-column max |word| the encode pass left in data->stats
+static int tc_block_digits(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, int *L) {
+	std::vector<uint64_t> st((data->d + 1) * 4);
+	P1_CUDA(cudaMemcpyAsync(st.data(), data->stats, st.size() * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	P1_CUDA(cudaStreamSynchronize(ctx->stream));
+	uint64_t maxabs = 0;
+	for(size_t c = col_lo; c < col_hi; c++) if(st[4 * c + 3] > maxabs) maxabs = st[4 * c + 3];
+	if(owns_target && st[4 * data->d + 3] > maxabs) maxabs = st[4 * data->d + 3];
+	*L = p1_tc_digits(maxabs, data->bits / 8);
+	return 0;
+}
+
+extern "C" int p1_gram_digits(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, int *digits) {
+	P1_CHECK(ctx && data && digits, "p1_gram_digits: arguments may not be null");
+	std::lock_guard<std::mutex> lock_(ctx->mu);
+	P1_CUDA(cudaSetDevice(ctx->device));
+	P1_CHECK(col_lo <= col_hi && col_hi <= data->d, "p1_gram_digits: invalid column range");
+	return tc_block_digits(ctx, data, col_lo, col_hi, owns_target, digits);
+}
+
 int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, uint64_t *acc_dev) {
 	tmap_encode_fn encode = get_tmap_encode();
 	P1_CHECK(encode, "p1_local_block: cuTensorMapEncodeTiled is not available from this driver");
@@ -358,22 +410,13 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	gs.nA = p1_nA(data->d);
 	const int WD = data->bits / 8;
 
-	// digits: from the per-column max |word| the encode pass left in data->stats
-	std::vector<uint64_t> st((data->d + 1) * 4);
-	P1_CUDA(cudaMemcpyAsync(st.data(), data->stats, st.size() * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-	P1_CUDA(cudaStreamSynchronize(ctx->stream));
-	uint64_t maxabs = 0;
-	for(int a = 0; a < gs.m; a++) {
-		size_t c = a < gs.mc ? col_lo + a : data->d;
-		if(st[4 * c + 3] > maxabs) maxabs = st[4 * c + 3];
-	}
-	const int L = p1_tc_digits(maxabs, WD);
+	int L = 0;
+	if(tc_block_digits(ctx, data, col_lo, col_hi, owns_target, &L)) return 1;
 	const int G = 2 * L - 1 < WD ? 2 * L - 1 : WD;
 
-	// digit planes P[l][a][row], rows padded to a whole K-block
+	// digit planes P[kblock][l][a][128 rows], rows padded to a whole K-block
 	const size_t ldp = p1_round_up(data->ld, TC_BK);
-	const size_t plane_stride = (size_t) gs.m * ldp;
-	const size_t need = plane_stride * L;
+	const size_t need = (size_t) gs.m * ldp * L;
 	if(ctx->limb_ws_bytes < need) {
 		if(ctx->limb_ws) {
 			P1_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -388,28 +431,29 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	{
 		dim3 grid((unsigned) ((ldp + 1023) / 1024), (unsigned) gs.m);
 		p1_prof_begin(ctx, P1_K_GRAM_LIMBS);
-		if(data->bits == 64) k_limb_split<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, gs, L, planes, ldp, plane_stride);
-		else k_limb_split<uint32_t><<<grid, 256, 0, ctx->stream>>>((const uint32_t *) data->xt, data->ld, gs, L, planes, ldp, plane_stride);
+		if(data->bits == 64) k_limb_split<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, gs, L, planes, ldp);
+		else k_limb_split<uint32_t><<<grid, 256, 0, ctx->stream>>>((const uint32_t *) data->xt, data->ld, gs, L, planes, ldp);
 		P1_LAUNCHED(ctx);
 	}
 
-	// tensor maps over the planes: dims (row, column, limb), u8, 128-byte swizzle
+	// tensor maps over the planes: dims (row in block, column, limb, block), u8, 128-byte swizzle
 	CUtensorMap mapA, mapB;
-	cuuint64_t gdim[3] = {(cuuint64_t) ldp, (cuuint64_t) gs.m, (cuuint64_t) L};
-	cuuint64_t gstr[2] = {(cuuint64_t) ldp, (cuuint64_t) plane_stride};
-	cuuint32_t estr[3] = {1, 1, 1};
-	cuuint32_t boxA[3] = {TC_BK, TC_BM, (cuuint32_t) L}, boxB[3] = {TC_BK, TC_BN, (cuuint32_t) L};
-	CUresult r1 = encode(&mapA, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstr, boxA, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+	// (declared as 32-bit elements: the swizzle and the bytes moved are the same as for u8)
+	static int esz = 0;
+	if(!esz) { const char *e = getenv("P1_TMA_ELEM"); esz = e ? atoi(e) : 4; }
+	const CUtensorMapDataType dt = esz == 8 ? CU_TENSOR_MAP_DATA_TYPE_UINT64 : esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+	cuuint64_t gdim[4] = {(cuuint64_t) (TC_BK / esz), (cuuint64_t) gs.m, (cuuint64_t) L, (cuuint64_t) (ldp / TC_BK)};
+	cuuint64_t gstr[3] = {TC_BK, (cuuint64_t) gs.m * TC_BK, (cuuint64_t) gs.m * TC_BK * L};
+	cuuint32_t estr[4] = {1, 1, 1, 1};
+	cuuint32_t boxA[4] = {(cuuint32_t) (TC_BK / esz), TC_BM, (cuuint32_t) L, 1}, boxB[4] = {(cuuint32_t) (TC_BK / esz), TC_BN, (cuuint32_t) L, 1};
+	CUresult r1 = encode(&mapA, dt, 4, planes, gdim, gstr, boxA, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 		CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-	CUresult r2 = encode(&mapB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstr, boxB, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+	CUresult r2 = encode(&mapB, dt, 4, planes, gdim, gstr, boxB, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 		CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	P1_CHECK(r1 == CUDA_SUCCESS && r2 == CUDA_SUCCESS, "p1_local_block: cuTensorMapEncodeTiled failed (%d, %d)", (int) r1, (int) r2);
 
 	TcParams P;
 	P.gs = gs;
-	P.L = L;
-	P.WD = WD;
-	P.G = G;
 	const size_t stage_bytes = (size_t) L * (TC_A_BYTES + TC_B_BYTES);
 	const size_t smem_budget = 220 * 1024;
 	int stages = (int) (smem_budget / stage_bytes);
@@ -435,10 +479,12 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	slices = (P.nblk + P.blk_per_cta - 1) / P.blk_per_cta;
 	P.acc = acc_dev;
 	const size_t smem = (size_t) stages * stage_bytes + 1024;
-	P1_CUDA(cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	tc_kernel_t kern = WD == 8 ? tc_kernel_for<8>(L) : tc_kernel_for<4>(L);
+	P1_CHECK(kern, "p1_local_block: no tcgen05 kernel for %d digits in a %d-byte ring", L, WD);
+	P1_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	dim3 grid((unsigned) tiles, (unsigned) slices);
 	p1_prof_begin(ctx, P1_K_GRAM_TC);
-	k_gram_tc<<<grid, TC_THREADS, smem, ctx->stream>>>(mapA, mapB, P);
+	kern<<<grid, TC_THREADS, smem, ctx->stream>>>(mapA, mapB, P);
 	P1_LAUNCHED(ctx);
 	return 0;
 }

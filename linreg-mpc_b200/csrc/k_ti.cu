@@ -109,7 +109,7 @@ int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
 #define TI_U 4 // stream blocks per lane per work unit
 
 #define TI_THREADS 1024         // register cap (launch bound); the launch uses TI_THREADS_DEFAULT
-#define TI_THREADS_DEFAULT 768  // leaves registers and thread slots on every SM for the HBM-bound party kernels of the other pipe
+#define TI_THREADS_DEFAULT 512  // leaves registers and thread slots on every SM for the HBM-bound party kernels of the other pipe
 
 struct TiParams {
 	AesCtrKey key;

@@ -415,8 +415,10 @@ extern "C" int p1_local_block(p1_ctx *ctx, const p1_data *data, size_t col_lo, s
 	size_t m = col_hi - col_lo + (owns_target ? 1 : 0);
 	if(m < 2) return 0;
 	if(algo == P1_GRAM_AUTO) {
-		// crossover measured on B200 (profiles/): the limb GEMM wins once the block fills a 128x128 tile
-		algo = P1_GRAM_IMAD;
+		// crossover measured on B200 (profiles/r1_kbench.txt): at n = 1M the limb GEMM (digit split included) already
+		// wins 3x at 32 columns; tiny blocks and tiny row counts stay on the CUDA-core kernel
+		size_t min_cols = ctx->opt_tc_min_cols > 0 ? (size_t) ctx->opt_tc_min_cols : 16;
+		algo = (m >= min_cols && data->n >= 4096) ? P1_GRAM_TCGEN05 : P1_GRAM_IMAD;
 	}
 	if(algo == P1_GRAM_TCGEN05) return p1_launch_gram_tc(ctx, data, col_lo, col_hi, owns_target, acc_dev);
 	P1_CHECK(algo == P1_GRAM_IMAD, "p1_local_block: unknown algo %d", algo);

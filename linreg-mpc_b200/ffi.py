@@ -49,6 +49,7 @@ SIGNATURES = {
     "p1_data_colmajor_dev": (c_vp, [c_vp, ctypes.POINTER(c_sz)]),
     "p1_acc_len": (c_sz, [c_sz]),
     "p1_local_block": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, c_vp, c_i]),
+    "p1_gram_digits": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, ctypes.POINTER(c_i)]),
     "p1_diag_sequential": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, c_vp]),
     "p1_ti_generate": (c_i, [c_vp, c_cp, c_u64, c_sz, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "p1_ti_values": (c_i, [c_vp, c_vp, c_vp, c_sz, c_vp, c_vp]),
