@@ -240,10 +240,9 @@ def main():
     cs = even_col_start(d, p)
     w = wl["bits_p1"] // 8
     # row shards: boundaries on multiples of 256 rows (16-byte aligned mask slices, whole OT tiles)
-    per = (n + world - 1) // world
-    per = (per + 255) // 256 * 256
-    row0 = min(rank * per, n)
-    n_rows = max(0, min(n, row0 + per) - row0)
+    from linreg_mpc_b200.phase1 import shard_rows
+    row0, n_rows = shard_rows(n, world, rank)
+    per = shard_rows(n, world, 0)[1]
     assert n_rows > 0, "more ranks than 256-row blocks"
 
     # synthetic instance per experiments/generate_tests.py:159-169 (X ~ N(0,1), columns scaled to

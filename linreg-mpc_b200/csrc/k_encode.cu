@@ -73,38 +73,58 @@ struct ColStats {
 };
 
 #define ENC_ROWS_PER_CTA 512
+#define ENC_TILE_ROWS 128     // rows per pass: 16 loads per thread in flight (32 KB per CTA)
 
-// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8)
+// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8).  A pass moves a 128-row x
+// 32-column tile: every thread issues its 16 source loads before the first use, and the
+// loads of the next pass are issued before the transposed stores of the current one
+// (software pipelining through registers), so ~32 KB per CTA stay in flight.
 template <typename W, typename SRC>
-__global__ void __launch_bounds__(256) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
+__global__ void __launch_bounds__(256, 2) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
 	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep) {
-	__shared__ W tile[32][33];
+	__shared__ W tile[ENC_TILE_ROWS][33];
+	constexpr int NL = ENC_TILE_ROWS / 8;        // loads per thread per pass
 	const int tx = threadIdx.x, ty = threadIdx.y;
 	const size_t c0 = (size_t) blockIdx.x * 32;
 	const size_t rbase = (size_t) blockIdx.y * ENC_ROWS_PER_CTA;
+	const size_t c_in = c0 + tx;
 	ColStats cs[4];
 #pragma unroll
 	for(int u = 0; u < 4; u++) cs[u].init();
-	for(int sub = 0; sub < ENC_ROWS_PER_CTA / 32; sub++) {
-		size_t r0 = rbase + (size_t) sub * 32;
+	SRC v[NL];
+	auto fetch = [&](size_t r0) {
+#pragma unroll
+		for(int u = 0; u < NL; u++) {
+			size_t r = r0 + ty + 8 * u;
+			v[u] = (r < rows && c_in < d) ? __ldcs(src + r * d + c_in) : (SRC) 0;
+		}
+	};
+	if(rbase < rows) fetch(rbase);
+	for(int sub = 0; sub < ENC_ROWS_PER_CTA / ENC_TILE_ROWS; sub++) {
+		size_t r0 = rbase + (size_t) sub * ENC_TILE_ROWS;
 		if(r0 >= rows) break;
 #pragma unroll
-		for(int u = 0; u < 4; u++) {
-			int rr = ty + 8 * u;
-			size_t r = r0 + rr, c = c0 + tx;
-			W wv = 0;
-			if(r < rows && c < d) wv = load_word<W, SRC>(src[r * d + c], ep);
-			tile[rr][tx] = wv;
+		for(int u = 0; u < NL; u++) {
+			size_t r = r0 + ty + 8 * u;
+			tile[ty + 8 * u][tx] = (r < rows && c_in < d) ? load_word<W, SRC>(v[u], ep) : (W) 0;
 		}
 		__syncthreads();
+		if(sub + 1 < ENC_ROWS_PER_CTA / ENC_TILE_ROWS && r0 + ENC_TILE_ROWS < rows) fetch(r0 + ENC_TILE_ROWS);
 #pragma unroll
 		for(int u = 0; u < 4; u++) {
 			int cc = ty + 8 * u;
-			size_t c = c0 + cc, r = r0 + tx;
-			if(c < d && r < rows) {
-				W wv = tile[tx][cc];
-				xt[c * ld + row_off + r] = wv;
-				cs[u].add<W>(wv);
+			size_t c = c0 + cc;
+			if(c < d) {
+				W *dst = xt + c * ld + row_off + r0;
+#pragma unroll
+				for(int j = 0; j < ENC_TILE_ROWS / 32; j++) {
+					int rr = tx + 32 * j;
+					if(r0 + rr < rows) {
+						W wv = tile[rr][cc];
+						dst[rr] = wv;
+						cs[u].add<W>(wv);
+					}
+				}
 			}
 		}
 		__syncthreads();

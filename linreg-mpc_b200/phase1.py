@@ -63,6 +63,48 @@ class Schedule:
         return n * (L + (3 * self.num_cross if masking else 0))
 
 
+def shard_rows(n_total, world, rank, align=256):
+    """Row shard of rank `rank`: equal slices whose boundaries fall on multiples
+    of `align` rows, so that every shard's slice of a mask stream is 16-byte aligned and
+    holds whole OT tiles (128/W rows); the last shards may be short or empty.
+    Returns (row0, n_rows)."""
+    per = (int(n_total) + world - 1) // world
+    per = (per + align - 1) // align * align
+    row0 = min(rank * per, int(n_total))
+    return row0, max(0, min(int(n_total), row0 + per) - row0)
+
+
+def ring_all_reduce(flat, group):
+    """Exact combination of the row shards' partial shares: every entry is a sum over rows in
+    Z_2^64 (a Z_2^32 share is the low half), so one wrapping integer sum all-reduce (NCCL over
+    NVLink on the GPU box, gloo in the CPU tests) is bit-exact in any reduction order."""
+    import torch.distributed as dist
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    return flat
+
+
+def chain_in_rank_order(step, width, group, device=None):
+    """The one quantity that is NOT order independent, the sequential double diagonal
+    (src/phase1.c:563-566): rank g continues the running sums of rank g-1 over its own rows
+    (`step(xy) -> xy`, numpy float64[width]) and hands them on; the last rank's result is
+    broadcast.  Returns the final float64[width] on every rank."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    gr = lambda r: dist.get_global_rank(group, r) if group is not None else r
+    buf = torch.zeros(width, dtype=torch.float64, device=device)
+    xy = np.zeros(width, dtype=np.float64)
+    if rank > 0:
+        dist.recv(buf, src=gr(rank - 1), group=group)
+        xy = buf.cpu().numpy().copy()
+    xy = np.ascontiguousarray(step(xy), dtype=np.float64)
+    buf.copy_(torch.from_numpy(xy))
+    if rank + 1 < world:
+        dist.send(buf, dst=gr(rank + 1), group=group)
+    dist.broadcast(buf, src=gr(world - 1), group=group)
+    return buf.cpu().numpy().copy()
+
+
 def _aes_ecb(key):
     from cryptography.hazmat.primitives.ciphers import Cipher, algorithms, modes
     return Cipher(algorithms.AES(bytes(key)), modes.ECB()).encryptor()
@@ -229,9 +271,8 @@ class Phase1Box:
         """exact ring combination of row shards: wrapping integer sum (NCCL over NVLink)"""
         if self.group is None:
             return
-        import torch.distributed as dist
         self.sync()
-        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+        ring_all_reduce(self.flat, self.group)
         self.torch.cuda.current_stream(self.dev).synchronize()
 
     def apply_values(self):
@@ -249,24 +290,14 @@ class Phase1Box:
         L.check(L.p1_acc_sub_values(ctx, ptr(self.acc), ptr(self.slot_b), ptr(self._vb), C))
 
     def _sequential_diag(self, lo, hi):
-        """literal double loop, chained over row shards in rank order (SURVEY.md §8e)"""
-        xy = np.zeros(hi - lo, dtype=np.float64)
-        if self.group is None:
+        """literal double loop, chained over row shards in rank order (SURVEY.md 8e)"""
+        def step(xy):
+            xy = np.ascontiguousarray(xy, dtype=np.float64)
             self.lib.check(self.lib.p1_diag_sequential(self.ctxs[0], self.data, lo, hi, self.precision, ptr(xy)))
             return xy
-        import torch.distributed as dist
-        t = self.torch
-        rank, world = dist.get_rank(self.group), dist.get_world_size(self.group)
-        buf = t.zeros(hi - lo, dtype=t.float64, device=self.dev)
-        if rank > 0:
-            dist.recv(buf, src=dist.get_global_rank(self.group, rank - 1), group=self.group)
-            xy = buf.cpu().numpy().copy()
-        self.lib.check(self.lib.p1_diag_sequential(self.ctxs[0], self.data, lo, hi, self.precision, ptr(xy)))
-        buf.copy_(t.from_numpy(xy))
-        if rank + 1 < world:
-            dist.send(buf, dst=dist.get_global_rank(self.group, rank + 1), group=self.group)
-        dist.broadcast(buf, src=dist.get_global_rank(self.group, world - 1), group=self.group)
-        return buf.cpu().numpy().copy()
+        if self.group is None:
+            return step(np.zeros(hi - lo, dtype=np.float64))
+        return chain_in_rank_order(step, hi - lo, self.group, self.dev)
 
     def finalize(self):
         """tail of run_party for every provider (src/phase1.c:605-641): returns
