@@ -406,6 +406,39 @@ def main():
         e2e = {"value": macs / (ms_e2e * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
 
+    # ---- --use_ot aggregation (BASELINE config 3 names it): a bounded sample of inner products over this
+    # rank's rows through the correlated-OT kernels, reported as COT/s with the extrapolation to all cross pairs
+    ot = None
+    if args.ot_sample > 0 and C:
+        from linreg_mpc_b200.phase1 import derive_cot_session, _bits128
+        L_, ctx0 = lib, box.ctxs[0]
+        s0_, s1_, delta_ = derive_cot_session(bytes(range(16, 32)), 3, 4)
+        chosen_ = np.where(_bits128(delta_)[:, None], s1_, s0_)
+        snd, rcv = ctypes.c_void_p(), ctypes.c_void_p()
+        L_.check(L_.p1_cot_sender_new(ctx0, delta_.tobytes(), pkg.ffi.ptr(np.ascontiguousarray(chosen_)), ctypes.byref(snd)))
+        L_.check(L_.p1_cot_receiver_new(ctx0, pkg.ffi.ptr(s0_), pkg.ffi.ptr(s1_), ctypes.byref(rcv)))
+        ub = torch.empty(int(L_.p1_cot_u_bytes(ctx0, n_rows)), dtype=torch.uint8, device=dev)
+        cb = torch.empty(int(L_.p1_cot_c_bytes(ctx0, n_rows)), dtype=torch.uint8, device=dev)
+        acc_ot = torch.zeros(box.acc_len, dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+
+        def ot_step():
+            for t in range(args.ot_sample):
+                L_.check(L_.p1_cot_receiver_extend(ctx0, rcv, box.data, d - 1, n, row0, pkg.ffi.ptr(ub)))
+                L_.check(L_.p1_cot_sender_step(ctx0, snd, box.data, t % (d // p), n, row0, pkg.ffi.ptr(ub), pkg.ffi.ptr(cb),
+                                               pkg.ffi.ptr(acc_ot), t))
+                L_.check(L_.p1_cot_receiver_finish(ctx0, rcv, pkg.ffi.ptr(cb), pkg.ffi.ptr(acc_ot), t))
+        ot_step()
+        ms_ot, _ = timed(ot_step, 2)
+        cots = args.ot_sample * n * wl["bits_p1"]
+        rate = cots / (ms_ot * 1e-3)
+        total_cots = C * n * wl["bits_p1"]
+        ot = {"inner_products": args.ot_sample, "cots": cots, "ms": ms_ot, "cot_per_s": rate,
+              "wire_bytes_per_cot": 16 + w, "all_cross_pairs_cots": total_cots, "all_cross_pairs_seconds_extrapolated": total_cots / rate,
+              "note": "reference protocol needs n*W correlated OTs per cross pair (src/phase1.c:58-65); reported, not the headline"}
+        L_.p1_cot_free(snd)
+        L_.p1_cot_free(rcv)
+
     # ---- parity property at full size: the providers' shares sum to the plain ring Gram of the encoded data
     check = None
     if rank == 0 and shares is not None:
@@ -437,7 +470,7 @@ def main():
                 "ring_macs_per_step": macs, "share_time_ms": ms_step, "wall_ms_per_step": ms_wall,
                 "gram_p1_equiv_macs": macs_gram_p1,
                 "gpu_launches": int(launches) * world, "kernels": kernels, "roofline": roofline, "clocks": clocks,
-                "e2e": e2e, "cpu_baseline": cpu, "check": check}
+                "e2e": e2e, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
         print(json.dumps(line))
     if group is not None:
         dist.destroy_process_group()

@@ -85,10 +85,13 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	return 0;
 }
 
+static void store_cache_drop(int device);
+
 extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 	if(!ctx) return;
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
+	store_cache_drop(ctx->device);
 	for(int i = 0; i < 2; i++) {
 		if(ctx->stage[i]) {
 			cudaFree(ctx->stage[i]);
@@ -235,6 +238,24 @@ extern "C" int p1_copy_d2h(p1_ctx *ctx, void *dst, const void *src, size_t bytes
 
 // ------------------------------------------------------------------ data
 
+// One retired column store per device is kept for the next p1_encode of the same size
+// (cudaMalloc/cudaFree of multi-GB buffers cost milliseconds and synchronise the device;
+// a provider re-encoding per run, and bench.py's step, hit this every time).
+struct StoreCache { void *xt; uint64_t *stats; size_t bytes, stat_bytes; };
+static StoreCache g_store[64] = {};
+static std::mutex g_store_mu;
+
+__global__ void k_zero_pads(unsigned char *__restrict__ xt, size_t col_bytes, size_t live_bytes, size_t cols) {
+	// zero bytes [live_bytes, col_bytes) of every column (rows >= n), 16 bytes per thread
+	const size_t pad = col_bytes - live_bytes, per = (pad + 15) / 16;
+	size_t t = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if(t >= per * cols) return;
+	size_t c = t / per, o = (t % per) * 16;
+	unsigned char *p = xt + c * col_bytes + live_bytes + o;
+	size_t k = pad - o < 16 ? pad - o : 16;
+	for(size_t i = 0; i < k; i++) p[i] = 0;
+}
+
 static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out) {
 	p1_data *dt = new p1_data();
 	dt->device = ctx->device;
@@ -245,16 +266,33 @@ static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out
 	dt->ld = p1_round_up(n ? n : 1, 256);
 	dt->xt = NULL;
 	dt->stats = NULL;
-	size_t bytes = (d + 1) * dt->ld * (size_t) (dt->bits / 8);
-	if(cudaMalloc(&dt->xt, bytes) != cudaSuccess || cudaMalloc(&dt->stats, (d + 1) * 4 * sizeof(uint64_t)) != cudaSuccess) {
+	const size_t w = (size_t) (dt->bits / 8);
+	size_t bytes = (d + 1) * dt->ld * w, stat_bytes = (d + 1) * 4 * sizeof(uint64_t);
+	{
+		std::lock_guard<std::mutex> l(g_store_mu);
+		StoreCache &c = g_store[ctx->device & 63];
+		if(c.xt && c.bytes == bytes && c.stat_bytes == stat_bytes) {
+			dt->xt = c.xt;
+			dt->stats = c.stats;
+			c.xt = NULL;
+			c.stats = NULL;
+		}
+	}
+	if(!dt->xt && (cudaMalloc(&dt->xt, bytes) != cudaSuccess || cudaMalloc(&dt->stats, stat_bytes) != cudaSuccess)) {
 		cudaError_t e = cudaGetLastError();
 		if(dt->xt) cudaFree(dt->xt);
 		delete dt;
 		return p1_fail("p1_encode: cannot allocate %zu bytes on device: %s", bytes, cudaGetErrorString(e));
 	}
-	// zero padding rows, the absent target column and the statistics
-	cudaMemsetAsync(dt->xt, 0, bytes, ctx->stream);
-	cudaMemsetAsync(dt->stats, 0, (d + 1) * 4 * sizeof(uint64_t), ctx->stream);
+	dt->bytes = bytes;
+	dt->stat_bytes = stat_bytes;
+	// zero the padding rows of every column, the absent target column and the statistics
+	if(dt->ld > n) {
+		size_t per = ((dt->ld - n) * w + 15) / 16, threads = per * (d + 1);
+		k_zero_pads<<<(unsigned) ((threads + 255) / 256), 256, 0, ctx->stream>>>((unsigned char *) dt->xt, dt->ld * w, n * w, d + 1);
+	}
+	if(!has_y) cudaMemsetAsync((char *) dt->xt + d * dt->ld * w, 0, dt->ld * w, ctx->stream);
+	cudaMemsetAsync(dt->stats, 0, stat_bytes, ctx->stream);
 	*out = dt;
 	return 0;
 }
@@ -263,9 +301,31 @@ extern "C" void p1_data_free(p1_data *dt) {
 	if(!dt) return;
 	cudaSetDevice(dt->device);
 	cudaDeviceSynchronize();
-	cudaFree(dt->xt);
-	cudaFree(dt->stats);
+	void *old_xt = NULL;
+	uint64_t *old_stats = NULL;
+	{
+		std::lock_guard<std::mutex> l(g_store_mu);
+		StoreCache &c = g_store[dt->device & 63];
+		old_xt = c.xt;
+		old_stats = c.stats;
+		c.xt = dt->xt;
+		c.stats = dt->stats;
+		c.bytes = dt->bytes;
+		c.stat_bytes = dt->stat_bytes;
+	}
+	if(old_xt) cudaFree(old_xt);
+	if(old_stats) cudaFree(old_stats);
 	delete dt;
+}
+
+// releases the retired column store of `device` (p1_ctx_destroy calls it)
+static void store_cache_drop(int device) {
+	std::lock_guard<std::mutex> l(g_store_mu);
+	StoreCache &c = g_store[device & 63];
+	if(c.xt) cudaFree(c.xt);
+	if(c.stats) cudaFree(c.stats);
+	c.xt = NULL;
+	c.stats = NULL;
 }
 
 extern "C" size_t p1_data_rows(const p1_data *dt) { return dt ? dt->n : 0; }

@@ -50,6 +50,7 @@ struct p1_data {
 	size_t ld;          // words between consecutive columns (n rounded up to 256)
 	void *xt;           // (d+1) x ld ring words, column-major; rows >= n are zero
 	uint64_t *stats;    // (d+1) x 4 : sq_lo, sq_hi, viol, maxabs
+	size_t bytes, stat_bytes;   // allocation sizes of xt and stats
 };
 
 // error plumbing (check() of the reference: message to stderr, return 1)
