@@ -389,6 +389,14 @@ def main():
             roofline["algorithmic_bytes_per_launch"] = alg_bytes[dominant] / max(kd["launches_per_step"], 1)
         if "lsu_bound" in kd:
             roofline["lsu_bound"] = kd["lsu_bound"]
+        try:   # DRAM bytes per launch of this kernel from the committed ncu --set full capture, if the shape matches
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                tr = json.load(f).get(dominant)
+            if tr and (dominant != "ti_generate" or (tr["pairs"] == batch and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"])):
+                roofline["traffic"] = tr["bytes_per_launch"]
+                roofline["traffic_source"] = tr["source"]
+        except (OSError, ValueError, KeyError):
+            pass
 
     # ---- end to end: host buffers in, shares out
     e2e = None
