@@ -116,20 +116,25 @@ struct AesSmemKey {            // one key per thread: sK[i * stride + t]
 	__byte_perm(__byte_perm(aes_lk<2, 0>(a, lb), aes_lk<0, 1>(b, lb), 0x0050), \
 	            __byte_perm(aes_lk<0, 2>(c, lb), aes_lk<1, 3>(d, lb), 0x7200), 0x7610)
 
-// rounds 2..10 on the state after round 1
-template <typename KA>
-__device__ __forceinline__ void aes_rounds_2_10(const KA &rk, uint32_t lb,
+// rounds R0..10 on the state after round R0-1
+template <int R0, typename KA>
+__device__ __forceinline__ void aes_rounds_to_10(const KA &rk, uint32_t lb,
 	uint32_t s0, uint32_t s1, uint32_t s2, uint32_t s3, uint32_t s[4]) {
-	uint32_t t0, t1, t2, t3;
 #pragma unroll
-	for(int r = 2; r < 10; r += 2) {
+	for(int r = R0; r < 10; r++) {
+		uint32_t t0, t1, t2, t3;
 		AES_ROUND(rk, r, s0, s1, s2, s3, t0, t1, t2, t3)
-		AES_ROUND(rk, r + 1, t0, t1, t2, t3, s0, s1, s2, s3)
+		s0 = t0; s1 = t1; s2 = t2; s3 = t3;
 	}
 	s[0] = AES_LAST(s0, s1, s2, s3) ^ rk(40);
 	s[1] = AES_LAST(s1, s2, s3, s0) ^ rk(41);
 	s[2] = AES_LAST(s2, s3, s0, s1) ^ rk(42);
 	s[3] = AES_LAST(s3, s0, s1, s2) ^ rk(43);
+}
+template <typename KA>
+__device__ __forceinline__ void aes_rounds_2_10(const KA &rk, uint32_t lb,
+	uint32_t s0, uint32_t s1, uint32_t s2, uint32_t s3, uint32_t s[4]) {
+	aes_rounds_to_10<2>(rk, lb, s0, s1, s2, s3, s);
 }
 
 // AES-128 encryption of the block (i0,i1,i2,i3) (little-endian words)
@@ -166,6 +171,44 @@ __device__ __forceinline__ void aes_ctr_block(const AesCtrKey &K, uint32_t lb, u
 		AES_ROUND(rk, 1, s0, s1, s2, s3, t0, t1, t2, t3)
 	}
 	aes_rounds_2_10(rk, lb, t0, t1, t2, t3, s);
+}
+
+// CTR blocks that agree in all counter bits above the low byte (a 256-block group) share
+// three of the four round-1 columns, hence 12 of the 16 round-2 lookups: they are kept in
+// registers (g) and a block of the group costs 1 + 4 lookups for rounds 1-2 instead of 20.
+struct AesCtrGroup {
+	uint32_t id;     // (uint32_t) block >> 8 of the group g belongs to; 0xffffffff = none
+	uint32_t g[4];   // round-2 output columns without the lookups of round-1 column 0 (includes rk[8..11])
+};
+
+__device__ __forceinline__ void aes_ctr_group(const AesCtrKey &K, uint32_t lb, uint32_t lo, AesCtrGroup &G) {
+	const uint32_t s3 = __byte_perm(lo, 0, 0x0123) ^ K.k.rk[3];
+	const uint32_t t1 = K.c1[1] ^ aes_lk<2, 2>(s3, lb);
+	const uint32_t t2 = K.c1[2] ^ aes_lk<1, 1>(s3, lb);
+	const uint32_t t3 = K.c1[3] ^ aes_lk<0, 0>(s3, lb);
+	G.g[0] = aes_lk<1, 1>(t1, lb) ^ aes_lk<2, 2>(t2, lb) ^ aes_lk<3, 3>(t3, lb) ^ K.k.rk[8];
+	G.g[1] = aes_lk<0, 0>(t1, lb) ^ aes_lk<1, 1>(t2, lb) ^ aes_lk<2, 2>(t3, lb) ^ K.k.rk[9];
+	G.g[2] = aes_lk<0, 0>(t2, lb) ^ aes_lk<1, 1>(t3, lb) ^ aes_lk<3, 3>(t1, lb) ^ K.k.rk[10];
+	G.g[3] = aes_lk<0, 0>(t3, lb) ^ aes_lk<2, 2>(t1, lb) ^ aes_lk<3, 3>(t2, lb) ^ K.k.rk[11];
+	G.id = lo >> 8;
+}
+
+// keystream block through the group cache G (one cache per stream a lane walks)
+__device__ __forceinline__ void aes_ctr_block_g(const AesCtrKey &K, uint32_t lb, uint64_t block, AesCtrGroup &G, uint32_t s[4]) {
+	const AesConstKey rk(K.k);
+	const uint32_t lo = (uint32_t) block;
+	if((uint32_t) (block >> 32) == K.hi) {
+		if((lo >> 8) != G.id) aes_ctr_group(K, lb, lo, G);
+		const uint32_t s3 = __byte_perm(lo, 0, 0x0123) ^ K.k.rk[3];
+		const uint32_t t0 = K.c1[0] ^ aes_lk<3, 3>(s3, lb);
+		const uint32_t u0 = G.g[0] ^ aes_lk<0, 0>(t0, lb);
+		const uint32_t u1 = G.g[1] ^ aes_lk<3, 3>(t0, lb);
+		const uint32_t u2 = G.g[2] ^ aes_lk<2, 2>(t0, lb);
+		const uint32_t u3 = G.g[3] ^ aes_lk<1, 1>(t0, lb);
+		aes_rounds_to_10<3>(rk, lb, u0, u1, u2, u3, s);
+	} else {
+		aes_ctr_block_k(rk, lb, block, s);
+	}
 }
 
 #endif

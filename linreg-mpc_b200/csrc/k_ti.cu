@@ -106,9 +106,9 @@ int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
 
 // ------------------------------------------------------------------ kernel
 
-#define TI_U 4 // stream blocks per lane per work unit
+#define TI_U 8 // stream blocks per lane per work unit: a unit is one 256-block group of the x stream (aes_dev.cuh, AesCtrGroup)
 
-#define TI_THREADS 1024         // register cap (launch bound); the launch uses TI_THREADS_DEFAULT
+#define TI_THREADS 512          // launch bound (128 registers); the launch uses TI_THREADS_DEFAULT or the ti_threads knob
 #define TI_THREADS_DEFAULT 512  // leaves registers and thread slots on every SM for the HBM-bound party kernels of the other pipe
 
 struct TiParams {
@@ -139,6 +139,8 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 	const uint64_t nbytes = P.n_rows * w;        // bytes of one mask on this shard
 	const uint64_t ydelta = P.n_total * w;       // stream distance x -> y
 	const uint32_t ysh = (uint32_t) (ydelta & 15);
+	AesCtrGroup gx, gy, gy1;                     // round-1/2 caches of the streams this lane walks
+	gx.id = gy.id = gy1.id = 0xffffffffu;
 
 	for(uint32_t u = gw; u < units; u += warps_total) {
 		const uint32_t p = u / P.units_per_pair, uu = u - p * P.units_per_pair;
@@ -150,20 +152,21 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 		uint64_t dot = 0;
 #pragma unroll 1
 		for(int i = 0; i < TI_U; i++) {
-			const uint64_t B = b_first + (uint64_t) uu * (32 * TI_U) + i * 32 + lane;
+			// units are the 256-aligned block groups of the x stream that overlap the shard's mask
+			const uint64_t B = (b_first & ~(uint64_t) 255) + (uint64_t) uu * (32 * TI_U) + i * 32 + lane;
 			const int64_t o = (int64_t) (B << 4) - (int64_t) X0; // byte offset of this block in the shard's mask
-			if(o >= (int64_t) nbytes) continue;                  // past the end (o > -16 always)
+			if(o <= -16 || o >= (int64_t) nbytes) continue;      // before the start / past the end
 			uint32_t xs[4] = {0, 0, 0, 0}, ys[4] = {0, 0, 0, 0};
-			if(need_x) aes_ctr_block(P.key, lb, B, xs);
+			if(need_x) aes_ctr_block_g(P.key, lb, B, gx, xs);
 			if(need_y) {
 				const uint64_t By = ((B << 4) + ydelta) >> 4;
 				if(ALIGNED) {
-					aes_ctr_block(P.key, lb, By, ys);
+					aes_ctr_block_g(P.key, lb, By, gy, ys);
 				} else {
 					// y bytes for these positions straddle two stream blocks
 					uint32_t ya[4], yb[4];
-					aes_ctr_block(P.key, lb, By, ya);
-					aes_ctr_block(P.key, lb, By + 1, yb);
+					aes_ctr_block_g(P.key, lb, By, gy, ya);
+					aes_ctr_block_g(P.key, lb, By + 1, gy1, yb);
 					const uint32_t ws = ysh >> 2; // whole 32-bit words (ysh is a multiple of w >= 4)
 #pragma unroll
 					for(int c = 0; c < 4; c++) {
@@ -261,7 +264,8 @@ extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, s
 	P.r = r_dev;
 	// stream blocks that can overlap one shard mask: bytes + up to 15 of misalignment
 	uint64_t nblk = ((uint64_t) n_rows * w + 15 + 15) / 16;
-	P.units_per_pair = (uint32_t) ((nblk + 32 * TI_U - 1) / (32 * TI_U));
+	// 256-aligned groups of stream blocks that can overlap the mask (its first block sits anywhere in a group)
+	P.units_per_pair = (uint32_t) ((nblk + 255 + 32 * TI_U - 1) / (32 * TI_U));
 	if(xy_dev) P1_CUDA(cudaMemsetAsync(xy_dev, 0, count * sizeof(uint64_t), ctx->stream));
 	bool aligned = ((uint64_t) n_total * w) % 16 == 0;
 	if(w == 8) return launch_ti<uint64_t>(ctx, P, aligned);

@@ -137,7 +137,7 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 	else if(!strcmp(name, "gram_tc_chunk_blocks")) ctx->opt_tc_chunk_blocks = value;
 	else if(!strcmp(name, "gram_tc_min_cols")) ctx->opt_tc_min_cols = value;
 	else if(!strcmp(name, "ti_threads")) {
-		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 1024), "ti_threads must be a multiple of 32 in [32,1024]");
+		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "ti_threads must be a multiple of 32 in [32,512]");
 		ctx->opt_ti_threads = value;
 	}
 	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
