@@ -69,6 +69,9 @@ enum {
 	P1_K_COT_SEND,        /* k_cot_tiles<sender> */
 	P1_K_COT_FINISH,      /* k_cot_finish */
 	P1_K_MISC,            /* k_acc_sub, k_ti_values */
+	P1_K_MSG_PACK,        /* k_pack_len / k_pack_scan / k_pack_write */
+	P1_K_MSG_UNPACK,      /* k_unpack_count / k_unpack_scan / k_unpack_write */
+	P1_K_SHARE_BITS,      /* k_share_bits */
 	P1_K_COUNT
 };
 int p1_ctx_profile(p1_ctx *ctx, int enable);
@@ -247,6 +250,41 @@ int p1_finalize(p1_ctx *ctx, const uint64_t *acc, size_t d, size_t col_lo, size_
                 int precision, int precision_p2, double normalizer2,
                 const double *diag_xy, int *need_sequential,
                 void **res_A, void **res_b);
+
+/* ------------------------------------------------------------------ f2: messages on the wire
+ * SecureMultiplication__Msg (src/protobuf/secure_multiplication{,_32}.proto):
+ *     message msg { repeated uintW vector = 1 [packed=true]; required uintW value = 2; }
+ * as protobuf-c's pack_to_buffer writes it in send_pmsg (src/phase1.c:131-139) and
+ * secure_multiplication__msg__unpack reads it in recv_pmsg (:111), for a batch of `count`
+ * messages whose vectors live on the GPU (the x / y masks of the TI, the party messages).
+ * proto2 wire bytes of one message:
+ *     [0x0A][varint payload_bytes][varint(vector[0]) .. varint(vector[n-1])]   (absent when n == 0)
+ *     [0x10][varint(value)]
+ * Message p occupies out_dev + p*stride_bytes; its length (the size_t that send_pmsg ships
+ * first, :133) is written to sizes_dev[p].  stride_bytes must be a multiple of 16 and at
+ * least p1_msg_max_bytes(ctx, n_words); buffers must be 16-byte aligned; vectors are ld_words
+ * apart (ld_words * word size a multiple of 16).  values: count uint64_t, host or device
+ * (the low W bits are used). */
+size_t p1_msg_max_bytes(const p1_ctx *ctx, size_t n_words);
+int p1_msg_pack(p1_ctx *ctx, const void *vec_dev, size_t ld_words, size_t n_words, size_t count,
+                const uint64_t *values, uint8_t *out_dev, size_t stride_bytes, uint64_t *sizes_dev);
+/* Inverse.  sizes: count uint64_t message lengths, host or device (each <= stride_bytes; the
+ * whole stride must be readable).  Every message must carry exactly n_words vector elements
+ * in the canonical form above (what protobuf-c emits); status_dev[p] = 0 on success, else a
+ * bit set of P1_MSG_* flags, and the caller falls back to its own parser for that message.
+ * Varints longer than W bits are truncated as protobuf parsers do. */
+#define P1_MSG_BAD_HEADER 1   /* first tag / payload length / trailer malformed or past the end */
+#define P1_MSG_BAD_COUNT 2    /* number of vector elements != n_words */
+#define P1_MSG_BAD_VARINT 4   /* an element longer than 10 bytes or cut off by the payload end */
+int p1_msg_unpack(p1_ctx *ctx, const uint8_t *in_dev, size_t stride_bytes, const uint64_t *sizes, size_t count,
+                  size_t n_words, void *vec_dev, size_t ld_words, uint64_t *values_dev, int32_t *status_dev);
+
+/* ------------------------------------------------------------------ f3: hand-off to phase 2
+ * The choice bits dcsSendIntArray builds from the shares (src/input.c:37-41):
+ *     sel[i*intsize + j] = (input[i] >> j) & 1,   intsize = FIXED_BIT_SIZE_P2
+ * one byte (C bool) per bit.  shares: n ufixed_t words (uint64_t or uint32_t per
+ * ring_bits_p2), host or device; sel: n * ring_bits_p2 bytes, host or device. */
+int p1_share_bits(p1_ctx *ctx, const void *shares, size_t n, uint8_t *sel);
 
 #ifdef __cplusplus
 }

@@ -69,6 +69,8 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->stage_bytes = 0;
 	ctx->limb_ws = NULL;
 	ctx->limb_ws_bytes = 0;
+	ctx->wire_ws = NULL;
+	ctx->wire_ws_bytes = 0;
 	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
 	ctx->opt_ti_threads = 0;
 	ctx->prof = false;
@@ -99,6 +101,7 @@ extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 		}
 	}
 	if(ctx->limb_ws) cudaFree(ctx->limb_ws);
+	if(ctx->wire_ws) cudaFree(ctx->wire_ws);
 	for(auto &r : ctx->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
 	for(auto e : ctx->prof_pool) cudaEventDestroy(e);
 	cudaFree(ctx->scratch);
@@ -176,7 +179,7 @@ void p1_prof_end(p1_ctx *ctx) {
 }
 
 static const char *const K_NAMES[P1_K_COUNT] = {"encode", "layout", "diag", "gram_imad", "gram_limbs", "gram_tc", "ti_generate",
-	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc"};
+	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc", "msg_pack", "msg_unpack", "share_bits"};
 
 extern "C" const char *p1_kernel_class_name(int c) { return c >= 0 && c < P1_K_COUNT ? K_NAMES[c] : NULL; }
 

@@ -26,6 +26,8 @@ struct p1_ctx {
 	void *stage[2]; size_t stage_bytes; cudaEvent_t stage_ev[2];
 	// tcgen05 Gram workspace (limb planes), grown on demand
 	void *limb_ws;  size_t limb_ws_bytes;
+	// tile sums / offsets of the wire-format kernels (k_wire.cu), grown on demand
+	void *wire_ws;  size_t wire_ws_bytes;
 	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols;
 	long opt_ti_threads;              // threads per CTA of k_ti_generate (0 = default)
 	// per-kernel-class event timing (p1_ctx_profile)

@@ -20,7 +20,9 @@ c_cp = ctypes.c_char_p
 P1_GRAM_AUTO, P1_GRAM_IMAD, P1_GRAM_TCGEN05 = 0, 1, 2
 # kernel classes of p1_ctx_profile_read (enum in include/p1gpu.h)
 (P1_K_ENCODE, P1_K_LAYOUT, P1_K_DIAG, P1_K_GRAM_IMAD, P1_K_GRAM_LIMBS, P1_K_GRAM_TC, P1_K_TI, P1_K_PARTY_B_MASK,
- P1_K_PARTY_A_STEP, P1_K_PARTY_B_SHARE, P1_K_COT_RECV, P1_K_COT_SEND, P1_K_COT_FINISH, P1_K_MISC, P1_K_COUNT) = range(15)
+ P1_K_PARTY_A_STEP, P1_K_PARTY_B_SHARE, P1_K_COT_RECV, P1_K_COT_SEND, P1_K_COT_FINISH, P1_K_MISC, P1_K_MSG_PACK, P1_K_MSG_UNPACK, P1_K_SHARE_BITS,
+ P1_K_COUNT) = range(18)
+P1_MSG_BAD_HEADER, P1_MSG_BAD_COUNT, P1_MSG_BAD_VARINT = 1, 2, 4
 
 # every symbol include/p1gpu.h declares, with its signature
 SIGNATURES = {
@@ -67,6 +69,10 @@ SIGNATURES = {
     "p1_cot_receiver_finish": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i64]),
     "p1_finalize": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_i, c_i, c_d, c_vp, c_vp,
                           ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
+    "p1_msg_max_bytes": (c_sz, [c_vp, c_sz]),
+    "p1_msg_pack": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp]),
+    "p1_msg_unpack": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz, c_sz, c_vp, c_sz, c_vp, c_vp]),
+    "p1_share_bits": (c_i, [c_vp, c_vp, c_sz, c_vp]),
 }
 
 

@@ -483,3 +483,93 @@ int p1o_write_instance(const char *path, const double *X, const double *y, size_
 	for(size_t i = 0; i < n; i++) fprintf(f, i + 1 < n ? "%.17g " : "%.17g\n", y[i]);
 	return fclose(f) ? 1 : 0;
 }
+
+/* ---------------- f2: SecureMultiplication__Msg on the wire ----------------
+ * src/protobuf/secure_multiplication{,_32}.proto:
+ *     message msg { repeated uintW vector = 1 [packed=true]; required uintW value = 2; }
+ * serialised by protobuf-c's generated pack_to_buffer (src/phase1.c:137-139) and parsed by
+ * secure_multiplication__msg__unpack (:111).  protobuf-c is a system package, absent from
+ * /root/reference; this restates the published proto2 wire format:
+ *     [0x0A][varint payload_bytes][varint(vector[0]) .. varint(vector[n-1])]   (omitted when n == 0)
+ *     [0x10][varint(value)]
+ * base-128 varints, least significant group first, MSB = continuation.  Pinned against the
+ * google.protobuf runtime by tests/golden/msg_wire.json (tests/golden/make_wire_golden.py). */
+
+static size_t vi_size(uint64_t v) {
+	size_t s = 1;
+	for(; v >= 0x80; v >>= 7) s++;
+	return s;
+}
+static size_t vi_put(uint8_t *out, uint64_t v) {
+	size_t s = 0;
+	for(; v >= 0x80; v >>= 7) out[s++] = (uint8_t) (v | 0x80);
+	out[s++] = (uint8_t) v;
+	return s;
+}
+
+size_t p1o_msg_packed_size(const void *vec, size_t n, uint64_t value, int bits) {
+	size_t payload = 0;
+	for(size_t i = 0; i < n; i++) payload += vi_size(ld(vec, i, bits));
+	return (n ? 1 + vi_size(payload) + payload : 0) + 1 + vi_size(ring(value, bits));
+}
+
+size_t p1o_msg_pack(const void *vec, size_t n, uint64_t value, int bits, uint8_t *out) {
+	size_t o = 0;
+	if(n) {
+		size_t payload = 0;
+		for(size_t i = 0; i < n; i++) payload += vi_size(ld(vec, i, bits));
+		out[o++] = 0x0A;
+		o += vi_put(out + o, payload);
+		for(size_t i = 0; i < n; i++) o += vi_put(out + o, ld(vec, i, bits));
+	}
+	out[o++] = 0x10;
+	o += vi_put(out + o, ring(value, bits));
+	return o;
+}
+
+/* varint of at most 10 bytes; bits above 64 are dropped as protobuf parsers do */
+static int vi_get(const uint8_t **p, const uint8_t *end, uint64_t *v) {
+	uint64_t r = 0;
+	for(int k = 0; k < 10; k++) {
+		if(*p >= end) return 0;
+		uint8_t b = *(*p)++;
+		if(7 * k < 64) r |= (uint64_t) (b & 0x7f) << (7 * k);
+		if(!(b & 0x80)) {
+			*v = r;
+			return 1;
+		}
+	}
+	return 0;
+}
+
+/* canonical form only (field 1 packed, then field 2).  Returns 0 on success; *n_out words
+ * are written to vec (capacity cap), the value to *value. */
+int p1o_msg_unpack(const uint8_t *in, size_t len, int bits, void *vec, size_t cap, size_t *n_out, uint64_t *value) {
+	const uint8_t *p = in, *end = in + len;
+	size_t n = 0;
+	uint64_t v;
+	if(p < end && *p == 0x0A) {
+		p++;
+		if(!vi_get(&p, end, &v) || v > (uint64_t) (end - p)) return 1;
+		const uint8_t *pe = p + v;
+		while(p < pe) {
+			if(!vi_get(&p, pe, &v)) return 1;
+			if(n >= cap) return 1;
+			st(vec, n++, bits, v);
+		}
+	}
+	if(p >= end || *p != 0x10) return 1;
+	p++;
+	if(!vi_get(&p, end, &v) || p != end) return 1;
+	*value = ring(v, bits);
+	*n_out = n;
+	return 0;
+}
+
+/* ---------------- f3: share hand-off to phase 2 (src/input.c:37-42) ----------------
+ * dcsSendIntArray: sel[i*intsize + j] = (input[i] >> j) & 1, intsize = FIXED_BIT_SIZE_P2,
+ * one bool (byte) per bit: the OT choice bits of the garbled-circuit input. */
+void p1o_share_bits(const void *shares, size_t n, int bits_p2, uint8_t *sel) {
+	for(size_t i = 0; i < n; i++)
+		for(int j = 0; j < bits_p2; j++) sel[i * (size_t) bits_p2 + j] = (uint8_t) ((ld(shares, i, bits_p2) >> j) & 1);
+}

@@ -90,6 +90,13 @@ class Oracle:
         L.p1o_run.restype = c_i
         L.p1o_write_instance.argtypes = [c_u8p, c_vp, c_vp, c_sz, c_sz, c_i, c_vp]
         L.p1o_write_instance.restype = c_i
+        L.p1o_msg_packed_size.argtypes = [c_vp, c_sz, c_u64, c_i]
+        L.p1o_msg_packed_size.restype = c_sz
+        L.p1o_msg_pack.argtypes = [c_vp, c_sz, c_u64, c_i, c_vp]
+        L.p1o_msg_pack.restype = c_sz
+        L.p1o_msg_unpack.argtypes = [c_vp, c_sz, c_i, c_vp, c_sz, c_vp, c_vp]
+        L.p1o_msg_unpack.restype = c_i
+        L.p1o_share_bits.argtypes = [c_vp, c_sz, c_i, c_vp]
         L.aes128_set_key.argtypes = [c_vp, c_u8p]
         L.aes128_force_portable.argtypes = [c_vp]
         L.aes128_ctr_keystream.argtypes = [c_vp, c_u64, c_vp, c_sz]
@@ -143,6 +150,32 @@ class Oracle:
         self.lib.p1o_ot_inner_product(session, _ptr(xs), 1, _ptr(xr), 1, n, bits,
                                       ctypes.byref(ss), ctypes.byref(sr), _ptr(u), _ptr(c))
         return (ss.value, sr.value, u, c) if want_wire else (ss.value, sr.value)
+
+    def msg_pack(self, vec, value, bits=64):
+        """SecureMultiplication__Msg{vector, value} -> proto2 wire bytes (src/phase1.c:137-139)"""
+        vec = np.ascontiguousarray(vec, dtype=word_dtype(bits))
+        size = self.lib.p1o_msg_packed_size(_ptr(vec), len(vec), int(value), bits)
+        out = np.zeros(size, dtype=np.uint8)
+        got = self.lib.p1o_msg_pack(_ptr(vec), len(vec), int(value), bits, _ptr(out))
+        assert got == size
+        return out
+
+    def msg_unpack(self, wire, bits=64, cap=None):
+        """wire bytes -> (vector, value), or None when malformed (src/phase1.c:111-112)"""
+        wire = np.ascontiguousarray(wire, dtype=np.uint8)
+        cap = len(wire) if cap is None else cap
+        vec = np.zeros(max(cap, 1), dtype=word_dtype(bits))
+        n, v = c_sz(), c_u64()
+        if self.lib.p1o_msg_unpack(_ptr(wire), len(wire), bits, _ptr(vec), cap, ctypes.byref(n), ctypes.byref(v)):
+            return None
+        return vec[:n.value].copy(), int(v.value)
+
+    def share_bits(self, shares, bits_p2=64):
+        """dcsSendIntArray's choice bits, src/input.c:41"""
+        shares = np.ascontiguousarray(shares, dtype=word_dtype(bits_p2))
+        sel = np.zeros(len(shares) * bits_p2, dtype=np.uint8)
+        self.lib.p1o_share_bits(_ptr(shares), len(shares), bits_p2, _ptr(sel))
+        return sel
 
     def write_instance(self, path, X, y, col_start):
         """fast C writer of the reference's input-file format (same text as write_instance below)"""

@@ -13,6 +13,7 @@ import pytest
 from oracle import pyoracle as po
 
 WIDTHS = [(64, 64, 56, 0), (32, 32, 24, 0), (64, 32, 56, 24)]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_aes_known_answer(oracle):
@@ -197,3 +198,41 @@ def test_cot_transpose_and_correlation(oracle):
             assert (s + r) % (1 << bits) == want
             assert u.size == 2048 * ((37 * bits + 127) // 128)
         oracle.lib.p1o_ot_session_free(ss)
+
+
+# --------------------------------------------------------------------------- f2 / f3
+def _wire_cases():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "msg_wire.json")) as f:
+        return json.load(f)["cases"]
+
+
+def test_msg_wire_matches_google_protobuf_golden(oracle):
+    """oracle pack/unpack against bytes serialised by the google.protobuf runtime
+    (tests/golden/make_wire_golden.py): the format protobuf-c emits in send_pmsg."""
+    cases = _wire_cases()
+    assert len(cases) >= 20
+    for c in cases:
+        bits, vec, val = c["bits"], [int(v) for v in c["vector"]], int(c["value"])
+        wire = oracle.msg_pack(np.array(vec, dtype=po.word_dtype(bits)), val, bits)
+        assert wire.tobytes().hex() == c["wire_hex"]
+        back = oracle.msg_unpack(np.frombuffer(bytes.fromhex(c["wire_hex"]), dtype=np.uint8), bits)
+        assert back is not None and [int(v) for v in back[0]] == vec and back[1] == val
+
+
+def test_msg_unpack_rejects_malformed(oracle):
+    good = oracle.msg_pack(np.array([1, 300, 2 ** 63], dtype=np.uint64), 9, 64)
+    assert oracle.msg_unpack(good, 64) is not None
+    assert oracle.msg_unpack(good[:-1], 64) is None                       # trailer cut
+    bad = good.copy(); bad[0] = 0x12
+    assert oracle.msg_unpack(bad, 64) is None                             # wrong first tag
+    bad = good.copy(); bad[1] += 1
+    assert oracle.msg_unpack(bad, 64) is None                             # payload length past the trailer
+    assert oracle.msg_unpack(np.concatenate([good, [0]]).astype(np.uint8), 64) is None  # trailing garbage
+
+
+def test_share_bits_is_lsb_first(oracle):
+    sel = oracle.share_bits(np.array([5, 1 << 63], dtype=np.uint64), 64)
+    assert sel.shape == (128,) and list(np.flatnonzero(sel)) == [0, 2, 64 + 63]
+    sel = oracle.share_bits(np.array([0x80000001], dtype=np.uint32), 32)
+    assert list(np.flatnonzero(sel)) == [0, 31]

@@ -6,6 +6,7 @@
   python tools/kbench.py gram   --n 1000000 --cols 500 --algo tcgen05|imad [--target]
   python tools/kbench.py encode --n 1000000 --cols 500
   python tools/kbench.py cot    --n 65536
+  python tools/kbench.py wire   --n 1000000 --pairs 33      (varint pack / unpack of masked vectors)
 
 Every case prints one JSON line: milliseconds per call (CUDA events on the context's
 stream, after warm-up) and the derived rate.  Buffers are far larger than the 126 MB L2
@@ -26,7 +27,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ti", "party", "gram", "encode", "cot"])
+    ap.add_argument("what", choices=["ti", "party", "gram", "encode", "cot", "wire"])
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=33)
     ap.add_argument("--cols", type=int, default=500)
@@ -167,6 +168,27 @@ def main():
         lib.p1_cot_free(snd)
         lib.p1_cot_free(rcv)
         lib.p1_data_free(data)
+    elif args.what == "wire":
+        vec = torch.empty(B * ld, dtype=wdt, device=dev).random_()
+        if w == 8:   # random_() leaves the sign bit clear: set it on half of the words like a real mask
+            vec ^= (torch.empty(B * ld, dtype=wdt, device=dev).random_() << 1)
+        stride = int(lib.p1_msg_max_bytes(ctx, n))
+        out = torch.empty(B * stride, dtype=torch.uint8, device=dev)
+        back = torch.empty(B * ld, dtype=wdt, device=dev)
+        sizes = torch.zeros(B, dtype=torch.int64, device=dev)
+        vals = torch.arange(B, dtype=torch.int64, device=dev)
+        vals2 = torch.zeros(B, dtype=torch.int64, device=dev)
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+        ms_p = timeit(lambda: lib.check(lib.p1_msg_pack(ctx, ptr(vec), ld, n, B, ptr(vals), ptr(out), stride, ptr(sizes))))
+        ms_u = timeit(lambda: lib.check(lib.p1_msg_unpack(ctx, ptr(out), stride, ptr(sizes), B, n, ptr(back), ld, ptr(vals2), ptr(status))))
+        torch.cuda.synchronize()
+        wire = int(sizes.sum().item())
+        ok = bool(torch.equal(back.view(B, ld)[:, :n], vec.view(B, ld)[:, :n])) and not bool(status.any().item())
+        res.update(pairs=B, wire_bytes=wire, bytes_per_word=wire / (B * n), round_trip_ok=ok,
+                   pack_ms=ms_p, pack_GBs=(B * n * w + wire) / ms_p / 1e6, pack_Gwords_s=B * n / ms_p / 1e6,
+                   unpack_ms=ms_u, unpack_GBs=(B * n * w + wire) / ms_u / 1e6, unpack_Gwords_s=B * n / ms_u / 1e6,
+                   note="GB/s = algorithmic bytes (words + wire bytes, each once) per second")
     print(json.dumps(res))
     lib.p1_ctx_destroy(ctx)
 
