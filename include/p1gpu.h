@@ -72,6 +72,7 @@ enum {
 	P1_K_MSG_PACK,        /* k_pack_len / k_pack_scan / k_pack_write */
 	P1_K_MSG_UNPACK,      /* k_unpack_count / k_unpack_scan / k_unpack_write */
 	P1_K_SHARE_BITS,      /* k_share_bits */
+	P1_K_TEXT,            /* k_tok_count / k_tok_scan* / k_tok_parse */
 	P1_K_COUNT
 };
 int p1_ctx_profile(p1_ctx *ctx, int enable);
@@ -285,6 +286,28 @@ int p1_msg_unpack(p1_ctx *ctx, const uint8_t *in_dev, size_t stride_bytes, const
  * one byte (C bool) per bit.  shares: n ufixed_t words (uint64_t or uint32_t per
  * ring_bits_p2), host or device; sel: n * ring_bits_p2 bytes, host or device. */
 int p1_share_bits(p1_ctx *ctx, const void *shares, size_t n, uint8_t *sel);
+
+/* ------------------------------------------------------------------ f4: text ingestion
+ * read_matrix / read_vector (src/linear.c:27-102) fscanf one "%lf" token at a time.  Here the
+ * whitespace-separated tokens of a text buffer are located with a prefix count and converted on
+ * the GPU (Eisel-Lemire decimal -> binary64: correctly rounded, i.e. the double glibc's strtod
+ * returns in the default rounding mode).
+ *   text       : `bytes` bytes, host or device (a device buffer must be 16-byte aligned)
+ *   out_dev    : max_tokens doubles on the device; token k -> out_dev[k]; tokens beyond
+ *                max_tokens are counted but not stored
+ *   n_tokens   : (host, out) number of tokens in the buffer
+ *   n_deferred : (host, out) number of tokens the kernel did not convert; they are stored as NaN
+ *                and the byte offsets of up to `cap` of them are written to `deferred`
+ *                (host, ascending; call again with a larger list if n_deferred > cap).  Deferred: anything that is not
+ *                [+-]digits[.digits][(e|E)[+-]digits] over the whole token (inf, nan, hex floats,
+ *                "localhost:1234"), tokens longer than 256 bytes, and mantissas of more than 19
+ *                digits whose truncation is ambiguous.  The caller converts those with its own
+ *                strtod and patches out_dev.
+ * The result feeds p1_encode directly.  For the reference's instance files, positioned at the X
+ * header (src/config.c:20): token 0, 1 = "n m", then n*m values of X (row-major), then "l", then
+ * l values of y.  Synchronises the stream. */
+int p1_parse_doubles(p1_ctx *ctx, const char *text, size_t bytes, double *out_dev, size_t max_tokens,
+                     uint64_t *n_tokens, uint64_t *n_deferred, uint64_t *deferred, size_t cap);
 
 #ifdef __cplusplus
 }

@@ -179,7 +179,7 @@ void p1_prof_end(p1_ctx *ctx) {
 }
 
 static const char *const K_NAMES[P1_K_COUNT] = {"encode", "layout", "diag", "gram_imad", "gram_limbs", "gram_tc", "ti_generate",
-	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc", "msg_pack", "msg_unpack", "share_bits"};
+	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc", "msg_pack", "msg_unpack", "share_bits", "text"};
 
 extern "C" const char *p1_kernel_class_name(int c) { return c >= 0 && c < P1_K_COUNT ? K_NAMES[c] : NULL; }
 

@@ -573,3 +573,42 @@ void p1o_share_bits(const void *shares, size_t n, int bits_p2, uint8_t *sel) {
 	for(size_t i = 0; i < n; i++)
 		for(int j = 0; j < bits_p2; j++) sel[i * (size_t) bits_p2 + j] = (uint8_t) ((ld(shares, i, bits_p2) >> j) & 1);
 }
+
+/* ---------------- f4: text ingestion (src/linear.c:27-102) ----------------
+ * read_matrix / read_vector consume the file with fscanf("%lf"): skip white space, then the
+ * longest prefix strtod accepts.  The restatement walks the white-space separated tokens and
+ * converts each with glibc's strtod (what fscanf uses); whole[k] tells whether strtod consumed
+ * the entire token with the plain decimal grammar (no inf / nan / hex float), which is the
+ * set the GPU path converts itself.  Returns the number of tokens. */
+#include <ctype.h>
+size_t p1o_parse_doubles(const char *text, size_t bytes, double *out, uint8_t *whole, size_t max_tokens) {
+	size_t k = 0, i = 0;
+	char tmp[512];
+	while(i < bytes) {
+		while(i < bytes && isspace((unsigned char) text[i])) i++;
+		if(i >= bytes) break;
+		size_t j = i;
+		while(j < bytes && !isspace((unsigned char) text[j])) j++;
+		if(k < max_tokens) {
+			size_t len = j - i;
+			int ok = len < sizeof(tmp);
+			double v = NAN;
+			if(ok) {
+				memcpy(tmp, text + i, len);
+				tmp[len] = 0;
+				char *end = NULL;
+				v = strtod(tmp, &end);
+				ok = end == tmp + len;
+				for(size_t c = 0; c < len && ok; c++) {
+					char ch = tmp[c];
+					if(!(isdigit((unsigned char) ch) || ch == '+' || ch == '-' || ch == '.' || ch == 'e' || ch == 'E')) ok = 0;
+				}
+			}
+			out[k] = v;
+			whole[k] = (uint8_t) ok;
+		}
+		k++;
+		i = j;
+	}
+	return k;
+}

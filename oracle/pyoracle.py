@@ -97,6 +97,8 @@ class Oracle:
         L.p1o_msg_unpack.argtypes = [c_vp, c_sz, c_i, c_vp, c_sz, c_vp, c_vp]
         L.p1o_msg_unpack.restype = c_i
         L.p1o_share_bits.argtypes = [c_vp, c_sz, c_i, c_vp]
+        L.p1o_parse_doubles.argtypes = [c_vp, c_sz, c_vp, c_vp, c_sz]
+        L.p1o_parse_doubles.restype = c_sz
         L.aes128_set_key.argtypes = [c_vp, c_u8p]
         L.aes128_force_portable.argtypes = [c_vp]
         L.aes128_ctr_keystream.argtypes = [c_vp, c_u64, c_vp, c_sz]
@@ -176,6 +178,15 @@ class Oracle:
         sel = np.zeros(len(shares) * bits_p2, dtype=np.uint8)
         self.lib.p1o_share_bits(_ptr(shares), len(shares), bits_p2, _ptr(sel))
         return sel
+
+    def parse_doubles(self, text):
+        """fscanf("%lf") token by token (src/linear.c:46,82): (values, whole-token flags)"""
+        buf = np.frombuffer(bytes(text), dtype=np.uint8)
+        cap = len(buf) // 2 + 1
+        out = np.zeros(cap, dtype=np.float64)
+        whole = np.zeros(cap, dtype=np.uint8)
+        n = self.lib.p1o_parse_doubles(_ptr(buf), len(buf), _ptr(out), _ptr(whole), cap)
+        return out[:n].copy(), whole[:n].astype(bool)
 
     def write_instance(self, path, X, y, col_start):
         """fast C writer of the reference's input-file format (same text as write_instance below)"""

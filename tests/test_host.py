@@ -83,3 +83,28 @@ def test_product_package_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".c", ".h", ".cpp")):
                 text = open(os.path.join(root, f)).read()
                 assert "pyoracle" not in text and "liboracle" not in text and "p1_oracle" not in text, f
+
+
+def test_pow5_table_is_current_and_conversion_matches_python_float():
+    """the Eisel-Lemire constants of k_text.cu (f4) are exactly what tools/gen_pow5_table.py
+    derives, and the integer restatement of the device conversion agrees with Python's
+    correctly rounded float() (the same result glibc's strtod gives fscanf("%lf"))."""
+    import random
+    import struct
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_pow5_table as g
+    lines = [l for l in open(os.path.join(ROOT, "linreg-mpc_b200", "csrc", "pow5_table.inc")) if l.startswith("{")]
+    assert len(lines) == len(g.TABLE) == 651
+    for l, t in zip(lines, g.TABLE):
+        hi, lo = (int(v, 16) for v in re.findall(r"0x([0-9a-f]{16})", l))
+        assert (hi << 64) | lo == t
+    rnd = random.Random(3)
+    for _ in range(20000):
+        w = rnd.randint(1, 10 ** rnd.randint(1, 19) - 1)
+        q = rnd.randint(-345, 310)
+        try:
+            want = float("%de%d" % (w, q))
+        except OverflowError:
+            want = float("inf")
+        assert struct.pack("<d", g.el_double(w, q)) == struct.pack("<d", want), (w, q)
