@@ -7,6 +7,7 @@
   python tools/kbench.py encode --n 1000000 --cols 500
   python tools/kbench.py cot    --n 65536
   python tools/kbench.py wire   --n 1000000 --pairs 33      (varint pack / unpack of masked vectors)
+  python tools/kbench.py text   --n 8000000                  (decimal text -> doubles, n tokens)
 
 Every case prints one JSON line: milliseconds per call (CUDA events on the context's
 stream, after warm-up) and the derived rate.  Buffers are far larger than the 126 MB L2
@@ -27,7 +28,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ti", "party", "gram", "encode", "cot", "wire"])
+    ap.add_argument("what", choices=["ti", "party", "gram", "encode", "cot", "wire", "text"])
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=33)
     ap.add_argument("--cols", type=int, default=500)
@@ -189,6 +190,25 @@ def main():
                    pack_ms=ms_p, pack_GBs=(B * n * w + wire) / ms_p / 1e6, pack_Gwords_s=B * n / ms_p / 1e6,
                    unpack_ms=ms_u, unpack_GBs=(B * n * w + wire) / ms_u / 1e6, unpack_Gwords_s=B * n / ms_u / 1e6,
                    note="GB/s = algorithmic bytes (words + wire bytes, each once) per second")
+    elif args.what == "text":
+        rng = np.random.default_rng(1)
+        x = rng.standard_normal(n)
+        raw = " ".join(map(repr, x.tolist())).encode()
+        tb = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        out = torch.empty(n, dtype=torch.float64, device=dev)
+        nt, nd = ctypes.c_uint64(), ctypes.c_uint64()
+        dl = np.zeros(16, np.uint64)
+        torch.cuda.synchronize()
+        lib.check(lib.p1_ctx_profile(ctx, 1))
+        for _ in range(args.reps):
+            lib.check(lib.p1_parse_doubles(ctx, ptr(tb), len(raw), ptr(out), n, ctypes.byref(nt), ctypes.byref(nd), ptr(dl), 16))
+        t, c = ctypes.c_double(), ctypes.c_uint64()
+        lib.check(lib.p1_ctx_profile_read(ctx, pkg.ffi.P1_K_TEXT, ctypes.byref(t), ctypes.byref(c)))
+        ms = t.value / args.reps
+        ok = bool(np.array_equal(out.cpu().numpy().view(np.uint64), x.view(np.uint64))) and nt.value == n and nd.value == 0
+        res.update(ms=ms, text_bytes=len(raw), tokens=n, exact=ok, text_GBs=len(raw) / ms / 1e6,
+                   GBs=(2 * len(raw) + 8 * n) / ms / 1e6, Gtokens_s=n / ms / 1e6,
+                   note="kernel time (events around the five launches); GBs = text read twice + doubles written")
     print(json.dumps(res))
     lib.p1_ctx_destroy(ctx)
 
