@@ -122,8 +122,9 @@ const void *p1_data_colmajor_dev(const p1_data *data, size_t *ld_words);
  * layout of the uint64_t accumulator every call below adds into (length p1_acc_len(d)):
  *     [0, nA)            share_A, packed lower triangle, idx(i,j) = i(i+1)/2 + j (src/linear.c:11-16)
  *     [nA, nA+d)         share_b
- *     [nA+d, nA+2d)      diagonal: low  32-bit halves summed: sum_k (word_k^2 & 0xffffffff)
- *     [nA+2d, nA+3d)     diagonal: high halves summed:        sum_k (word_k^2 >> 32)
+ *     [nA+d, nA+2d)      diagonal: sum of squares, low part  } two sums of 32-bit halves of partial sums;
+ *     [nA+2d, nA+3d)     diagonal: sum of squares, high part } (high << 32) + low = sum_k word_k^2 exactly
+ *                                                              whenever the next entry is 0
  *     [nA+3d, nA+4d)     diagonal: number of rows with |word| >= 2^26
  * All entries are sums over rows, so row shards combine by a wrapping u64 all-reduce. */
 size_t p1_acc_len(size_t d);

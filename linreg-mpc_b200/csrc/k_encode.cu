@@ -41,23 +41,26 @@ template <> __device__ __forceinline__ uint32_t load_word<uint32_t, double>(doub
 template <> __device__ __forceinline__ uint64_t load_word<uint64_t, uint64_t>(uint64_t v, const EncodeParams &) { return v; }
 template <> __device__ __forceinline__ uint32_t load_word<uint32_t, uint32_t>(uint32_t v, const EncodeParams &) { return v; }
 
+// Per-column statistics of one thread.  sq = sum of (low 32 bits of |word|)^2: the exact sum of
+// squares whenever no |word| reaches 2^26 (viol == 0), which is the only case its consumers
+// (p1_finalize's exact diagonal) use it; it is flushed as two 32-bit halves so that the
+// 64-bit accumulator entries cannot wrap when row shards and CTAs are summed.
 struct ColStats {
-	uint64_t lo, hi, viol, mx;
-	__device__ __forceinline__ void init() { lo = hi = viol = mx = 0; }
+	uint64_t sq, mx;
+	uint32_t viol;
+	__device__ __forceinline__ void init() { sq = mx = 0; viol = 0; }
 	template <typename W> __device__ __forceinline__ void add(W word) {
 		typedef typename p1_word<W>::s S;
-		int64_t s = (int64_t) (S) word;
-		uint64_t a = s < 0 ? (uint64_t) 0 - (uint64_t) s : (uint64_t) s;
-		uint64_t sq = a * a;
-		lo += sq & 0xffffffffull;
-		hi += sq >> 32;
-		viol += (a >> P1_SQ_LIMIT_BITS) ? 1 : 0;
+		const int64_t s = (int64_t) (S) word;
+		const uint64_t a = s < 0 ? (uint64_t) 0 - (uint64_t) s : (uint64_t) s;
+		const uint32_t a32 = (uint32_t) a;
+		sq += (uint64_t) a32 * a32;                     // one IMAD.WIDE.U32 with accumulate
+		viol += (a >> P1_SQ_LIMIT_BITS) ? 1u : 0u;
 		mx = a > mx ? a : mx;
 	}
 	__device__ __forceinline__ void warp_reduce() {
-		lo = p1_warp_sum(lo);
-		hi = p1_warp_sum(hi);
-		viol = p1_warp_sum(viol);
+		sq = p1_warp_sum(sq);
+		viol = __reduce_add_sync(0xffffffffu, viol);
 #pragma unroll
 		for(int o = 16; o; o >>= 1) {
 			uint64_t t = __shfl_xor_sync(0xffffffffu, mx, o);
@@ -65,9 +68,9 @@ struct ColStats {
 		}
 	}
 	__device__ __forceinline__ void flush(uint64_t *st) {
-		p1_red_add(st + 0, lo);
-		p1_red_add(st + 1, hi);
-		if(viol) p1_red_add(st + 2, viol);
+		p1_red_add(st + 0, sq & 0xffffffffull);
+		p1_red_add(st + 1, sq >> 32);
+		if(viol) p1_red_add(st + 2, (uint64_t) viol);
 		atomicMax(reinterpret_cast<unsigned long long *>(st + 3), (unsigned long long) mx);
 	}
 };
@@ -75,15 +78,17 @@ struct ColStats {
 #define ENC_ROWS_PER_CTA 512
 #define ENC_TILE_ROWS 128     // rows per pass: 16 loads per thread in flight (32 KB per CTA)
 
-// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8).  A pass moves a 128-row x
-// 32-column tile: every thread issues its 16 source loads before the first use, and the
-// loads of the next pass are issued before the transposed stores of the current one
-// (software pipelining through registers), so ~32 KB per CTA stay in flight.
-template <typename W, typename SRC>
-__global__ void __launch_bounds__(256, 2) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
-	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep) {
-	__shared__ W tile[ENC_TILE_ROWS][33];
+// One CTA: ENC_ROWS_PER_CTA rows x 32 columns.  A pass moves a 128-row x 32-column tile: every
+// thread issues its 16 source loads before the first use, and the loads of the next pass are
+// issued before the transposed stores of the current one (software pipelining through
+// registers), so ~32 KB per CTA stay in flight.  FULL = the CTA's rows and columns all exist:
+// no bounds tests, addresses by pointer increments (the integer pipe, not HBM, was the limit
+// with per-element tests and 64-bit index products: profiles/r1g_new_kernels_full.txt).
+template <typename W, typename SRC, bool FULL>
+__device__ __forceinline__ void enc_cta(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, const EncodeParams &ep, W (*tile)[33]) {
 	constexpr int NL = ENC_TILE_ROWS / 8;        // loads per thread per pass
+	constexpr int NSUB = ENC_ROWS_PER_CTA / ENC_TILE_ROWS;
 	const int tx = threadIdx.x, ty = threadIdx.y;
 	const size_t c0 = (size_t) blockIdx.x * 32;
 	const size_t rbase = (size_t) blockIdx.y * ENC_ROWS_PER_CTA;
@@ -92,49 +97,65 @@ __global__ void __launch_bounds__(256, 2) k_rows_to_cols(const SRC *__restrict__
 #pragma unroll
 	for(int u = 0; u < 4; u++) cs[u].init();
 	SRC v[NL];
+	const size_t step = 8 * d;
+	const SRC *ip = src + (rbase + ty) * d + c_in;       // next element this thread loads
 	auto fetch = [&](size_t r0) {
 #pragma unroll
 		for(int u = 0; u < NL; u++) {
-			size_t r = r0 + ty + 8 * u;
-			v[u] = (r < rows && c_in < d) ? __ldcs(src + r * d + c_in) : (SRC) 0;
+			if(FULL) v[u] = __ldcs(ip);
+			else v[u] = (r0 + ty + 8 * u < rows && c_in < d) ? __ldcs(ip) : (SRC) 0;
+			ip += step;
 		}
 	};
-	if(rbase < rows) fetch(rbase);
-	for(int sub = 0; sub < ENC_ROWS_PER_CTA / ENC_TILE_ROWS; sub++) {
-		size_t r0 = rbase + (size_t) sub * ENC_TILE_ROWS;
-		if(r0 >= rows) break;
+	fetch(rbase);
+	W *op[4];
+#pragma unroll
+	for(int u = 0; u < 4; u++) op[u] = xt + (c0 + ty + 8 * u) * ld + row_off + rbase + tx;
+#pragma unroll 1
+	for(int sub = 0; sub < NSUB; sub++) {
+		const size_t r0 = rbase + (size_t) sub * ENC_TILE_ROWS;
+		if(!FULL && r0 >= rows) break;
 #pragma unroll
 		for(int u = 0; u < NL; u++) {
-			size_t r = r0 + ty + 8 * u;
-			tile[ty + 8 * u][tx] = (r < rows && c_in < d) ? load_word<W, SRC>(v[u], ep) : (W) 0;
+			if(FULL) tile[ty + 8 * u][tx] = load_word<W, SRC>(v[u], ep);
+			else tile[ty + 8 * u][tx] = (r0 + ty + 8 * u < rows && c_in < d) ? load_word<W, SRC>(v[u], ep) : (W) 0;
 		}
 		__syncthreads();
-		if(sub + 1 < ENC_ROWS_PER_CTA / ENC_TILE_ROWS && r0 + ENC_TILE_ROWS < rows) fetch(r0 + ENC_TILE_ROWS);
+		if(sub + 1 < NSUB && (FULL || r0 + ENC_TILE_ROWS < rows)) fetch(r0 + ENC_TILE_ROWS);
 #pragma unroll
 		for(int u = 0; u < 4; u++) {
-			int cc = ty + 8 * u;
-			size_t c = c0 + cc;
-			if(c < d) {
-				W *dst = xt + c * ld + row_off + r0;
+			const int cc = ty + 8 * u;
+			if(FULL || c0 + cc < d) {
 #pragma unroll
 				for(int j = 0; j < ENC_TILE_ROWS / 32; j++) {
-					int rr = tx + 32 * j;
-					if(r0 + rr < rows) {
-						W wv = tile[rr][cc];
-						dst[rr] = wv;
+					const int rr = tx + 32 * j;
+					if(FULL || r0 + rr < rows) {
+						const W wv = tile[rr][cc];
+						op[u][32 * j] = wv;
 						cs[u].add<W>(wv);
 					}
 				}
 			}
+			op[u] += ENC_TILE_ROWS;
 		}
 		__syncthreads();
 	}
 #pragma unroll
 	for(int u = 0; u < 4; u++) {
 		cs[u].warp_reduce();
-		size_t c = c0 + ty + 8 * u;
+		const size_t c = c0 + ty + 8 * u;
 		if(tx == 0 && c < d) cs[u].flush(stats + 4 * c);
 	}
+}
+
+// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8)
+template <typename W, typename SRC>
+__global__ void __launch_bounds__(256, 2) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep) {
+	__shared__ W tile[ENC_TILE_ROWS][33];
+	const bool full = (size_t) blockIdx.x * 32 + 32 <= d && (size_t) blockIdx.y * ENC_ROWS_PER_CTA + ENC_ROWS_PER_CTA <= rows;
+	if(full) enc_cta<W, SRC, true>(src, rows, d, row_off, xt, ld, stats, ep, tile);
+	else enc_cta<W, SRC, false>(src, rows, d, row_off, xt, ld, stats, ep, tile);
 }
 
 template <typename W, typename SRC>
