@@ -230,6 +230,7 @@ def main():
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version / debug lines stay off stdout: ONE JSON line there
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
 

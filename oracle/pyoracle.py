@@ -33,6 +33,9 @@ def build(ref=True):
     subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
     if ref and os.path.isdir(REFERENCE_SRC):
         subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+        if os.path.exists(os.path.join(HERE, "..", "linreg-mpc_b200", "libp1gpu.so")):
+            # the product's host file needs the reference's headers too: built here, travels prebuilt
+            subprocess.check_call(["make", "-s", "-C", HERE, "gpuhost"])
 
 
 def word_dtype(bits):
@@ -212,8 +215,11 @@ class Oracle:
 class RefLib:
     """The reference's own phase 1 (see oracle/ref_shims/ref_driver.c)."""
 
-    def __init__(self, bits_p1=64, bits_p2=64):
-        path = os.path.join(HERE, "_ref", "libp1ref_%d_%d.so" % (bits_p1, bits_p2))
+    def __init__(self, bits_p1=64, bits_p2=64, gpuhost=False):
+        """gpuhost=True: the same driver and shims around linreg-mpc_b200/host/phase1_gpu.c (the
+        product's run_party / run_trusted_initializer on top of libp1gpu.so) instead of the
+        reference's phase1.c - the drop-in under test, not the checker."""
+        path = os.path.join(HERE, "_ref", "libp1%s_%d_%d.so" % ("gpuhost" if gpuhost else "ref", bits_p1, bits_p2))
         if not os.path.exists(path):
             build(ref=True)
         L = self.lib = ctypes.CDLL(path)
@@ -233,8 +239,8 @@ class RefLib:
         assert L.p1ref_bits_p1() == bits_p1 and L.p1ref_bits_p2() == bits_p2
 
     @staticmethod
-    def available(bits_p1=64, bits_p2=64):
-        return os.path.exists(os.path.join(HERE, "_ref", "libp1ref_%d_%d.so" % (bits_p1, bits_p2)))
+    def available(bits_p1=64, bits_p2=64, gpuhost=False):
+        return os.path.exists(os.path.join(HERE, "_ref", "libp1%s_%d_%d.so" % ("gpuhost" if gpuhost else "ref", bits_p1, bits_p2)))
 
     def run(self, path, d, num_dp, precision, precision_p2=0, use_ot=False, ti_key=TI_KEY, ot_key=OT_KEY):
         P = num_dp + 2

@@ -360,3 +360,31 @@ void secure_multiplication__msg__free_unpacked(SecureMultiplication__Msg *m, Pro
 	free(m->vector);
 	free(m);
 }
+
+/* ------------------------------------------------------------------ */
+/* hooks of linreg-mpc_b200/host/phase1_gpu.c (strong definitions override its weak ones):  */
+/* the same injected keys as the stand-ins above, so that the GPU host file and the           */
+/* reference's phase1.c produce the same share words in the loop-back driver.                 */
+/* ------------------------------------------------------------------ */
+
+int p1host_ti_key(uint8_t key[16]) {
+	memcpy(key, g_ti_key, 16);
+	return 0;
+}
+
+int p1host_base_ot(ProtocolDesc *pd, int sender_party, int receiver_party, int role,
+	uint8_t seeds0[128][16], uint8_t seeds1[128][16], uint8_t delta[16]) {
+	(void) pd;
+	uint8_t s0[COT_KAPPA][16], s1[COT_KAPPA][16], dl[16];
+	cot_session_derive(g_ot_key, sender_party, receiver_party, s0, s1, dl);
+	if(role) {   /* sender: Delta and k_i^{Delta_i} */
+		memcpy(delta, dl, 16);
+		for(int i = 0; i < COT_KAPPA; i++) memcpy(seeds0[i], ((dl[i / 8] >> (i % 8)) & 1) ? s1[i] : s0[i], 16);
+		memset(seeds1, 0, COT_KAPPA * 16);
+	} else {     /* receiver: both seeds of every base OT */
+		memcpy(seeds0, s0, sizeof(s0));
+		memcpy(seeds1, s1, sizeof(s1));
+		memset(delta, 0, 16);
+	}
+	return 0;
+}

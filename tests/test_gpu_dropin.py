@@ -1,0 +1,75 @@
+"""The drop-in itself: linreg-mpc_b200/host/phase1_gpu.c exports the reference's own entry points
+(run_trusted_initializer / run_party, src/phase1.h:14-29).  Built against the reference's headers and
+the loop-back shims, it runs every party of an instance as a thread - exactly like the build of the
+reference's unmodified phase1.c next to it (oracle/_ref) - with all arithmetic, the text ingestion and
+the protobuf (de)serialisation on the GPU.  Every share word of every provider must equal the
+reference's, and the bytes on every socket must add up to the same totals."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+CASES = [  # b1, b2, precision, precision_p2
+    (64, 64, 56, 0), (32, 32, 24, 0), (64, 32, 56, 24)]
+
+
+def both(path, d, num_dp, b1, b2, prec, prec2, use_ot):
+    if not (po.RefLib.available(b1, b2) and po.RefLib.available(b1, b2, gpuhost=True)):
+        pytest.skip("oracle/_ref was not prebuilt (needs the reference sources: build container only)")
+    ref = po.RefLib(b1, b2).run(path, d, num_dp, prec, prec2, use_ot=use_ot)
+    gpu = po.RefLib(b1, b2, gpuhost=True).run(path, d, num_dp, prec, prec2, use_ot=use_ot)
+    return ref, gpu
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", CASES)
+def test_run_party_masking_matches_reference(p1lib, tmp_path, b1, b2, prec, prec2, monkeypatch):
+    monkeypatch.setenv("P1GPU_BATCH", "3")            # runs of 4 columns -> batches of 3 + 1
+    n, d, cs = 1500, 12, [0, 4, 8]
+    X, y, _ = po.generate_lin_regression(n, d, seed=21)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, rsent), (gs, _, gsent) = both(path, d, len(cs), b1, b2, prec, prec2, False)
+    assert np.array_equal(gs, rs)
+    assert np.array_equal(gsent, rsent), "bytes per socket differ from the reference's"
+
+
+def test_run_party_matches_committed_reference_golden(p1lib, golden, tmp_path):
+    """tests/golden/phase1_ref_shares.json: share words (and bytes per socket in masking mode) the
+    reference's own phase1.c produced for examples/readme_example.in and the other committed
+    instances, every width combination, masking and --use_ot"""
+    ran = 0
+    for k, c in enumerate(golden["cases"]):
+        if not po.RefLib.available(c["bits_p1"], c["bits_p2"], gpuhost=True):
+            pytest.skip("oracle/_ref/libp1gpuhost_* was not prebuilt (needs the reference headers: build container only)")
+        path = str(tmp_path / ("g%d.in" % k))
+        po.write_instance(path, c["X"], c["y"], c["col_start"])
+        gs, _, sent = po.RefLib(c["bits_p1"], c["bits_p2"], gpuhost=True).run(
+            path, c["d"], len(c["col_start"]), c["precision"], c["precision_p2"], use_ot=c["use_ot"],
+            ti_key=golden["ti_key"], ot_key=golden["ot_key"])
+        assert np.array_equal(gs, c["shares"]), "case %d (%s, use_ot=%s)" % (k, c["instance"], c["use_ot"])
+        if not c["use_ot"]:
+            assert np.array_equal(sent, np.array(c["bytes_sent"], dtype=np.uint64).reshape(sent.shape))
+        ran += 1
+    assert ran >= 6
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", CASES)
+def test_run_party_use_ot_matches_reference(p1lib, tmp_path, b1, b2, prec, prec2):
+    n, d, cs = 130, 5, [0, 2, 4]      # three providers: both role assignments of :392 occur
+    X, y, _ = po.generate_lin_regression(n, d, seed=22)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, _), (gs, _, _) = both(path, d, len(cs), b1, b2, prec, prec2, True)
+    assert np.array_equal(gs, rs)
+
+
+def test_run_party_large_vectors_sequential_diagonal(p1lib, tmp_path):
+    """words above 2^26 (tiny n): the exact diagonal shortcut does not apply and the literal loop runs"""
+    n, d, cs = 40, 6, [0, 3]
+    X, y, _ = po.generate_lin_regression(n, d, seed=23)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, _), (gs, _, _) = both(path, d, len(cs), 64, 64, 56, 0, False)
+    assert np.array_equal(gs, rs)
