@@ -90,6 +90,9 @@ int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
 int p1_dev_free(p1_ctx *ctx, void *dev);
 int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes);
+/* page-locked host memory for buffers that cross PCIe every message (full-rate, truly asynchronous copies) */
+int p1_host_alloc(p1_ctx *ctx, size_t bytes, void **host);
+int p1_host_free(p1_ctx *ctx, void *host);
 int p1_copy_h2d(p1_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
 int p1_copy_d2h(p1_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes); /* synchronises */
 

@@ -227,6 +227,18 @@ extern "C" int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes) {
 	P1_CUDA(cudaMemsetAsync(dev, 0, bytes, ctx->stream));
 	return 0;
 }
+extern "C" int p1_host_alloc(p1_ctx *ctx, size_t bytes, void **host) {
+	P1_ENTER(ctx);
+	P1_CHECK(host, "p1_host_alloc: null output");
+	*host = NULL;
+	P1_CUDA(cudaHostAlloc(host, bytes ? bytes : 1, cudaHostAllocDefault));
+	return 0;
+}
+extern "C" int p1_host_free(p1_ctx *ctx, void *host) {
+	P1_ENTER(ctx);
+	if(host) P1_CUDA(cudaFreeHost(host));
+	return 0;
+}
 extern "C" int p1_copy_h2d(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
 	P1_ENTER(ctx);
 	P1_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));

@@ -40,6 +40,8 @@ SIGNATURES = {
     "p1_dev_alloc": (c_i, [c_vp, c_sz, ctypes.POINTER(c_vp)]),
     "p1_dev_free": (c_i, [c_vp, c_vp]),
     "p1_dev_zero": (c_i, [c_vp, c_vp, c_sz]),
+    "p1_host_alloc": (c_i, [c_vp, c_sz, ctypes.POINTER(c_vp)]),
+    "p1_host_free": (c_i, [c_vp, c_vp]),
     "p1_copy_h2d": (c_i, [c_vp, c_vp, c_vp, c_sz]),
     "p1_copy_d2h": (c_i, [c_vp, c_vp, c_vp, c_sz]),
     "p1_encode": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, c_d, c_i, ctypes.POINTER(c_vp)]),

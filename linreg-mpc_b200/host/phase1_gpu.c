@@ -116,7 +116,7 @@ static void bufs_free(gpu_bufs *g) {
 	for(int k = 0; k < 3; k++) if(g->vec[k]) p1_dev_free(g->ctx, g->vec[k]);
 	void *dv[] = {g->wire_dev, g->sizes_dev, g->vals_dev, g->vals2_dev, g->zero_dev, g->status_dev};
 	for(size_t k = 0; k < sizeof(dv) / sizeof(dv[0]); k++) if(dv[k]) p1_dev_free(g->ctx, dv[k]);
-	free(g->wire_host);
+	if(g->wire_host) p1_host_free(g->ctx, g->wire_host);
 	free(g->sizes_host);
 	free(g->status_host);
 	p1_ctx_destroy(g->ctx);
@@ -138,10 +138,10 @@ static int bufs_init(gpu_bufs *g, size_t n, int nvec) {
 	GCHECK(p1_dev_alloc(g->ctx, g->batch * 8, (void **) &g->zero_dev));
 	GCHECK(p1_dev_zero(g->ctx, g->zero_dev, g->batch * 8));
 	GCHECK(p1_dev_alloc(g->ctx, g->batch * 4, (void **) &g->status_dev));
-	g->wire_host = malloc(g->batch * g->stride);
+	GCHECK(p1_host_alloc(g->ctx, g->batch * g->stride, (void **) &g->wire_host));
 	g->sizes_host = calloc(g->batch, 8);
 	g->status_host = calloc(g->batch, 4);
-	check(g->wire_host && g->sizes_host && g->status_host, "malloc: %s", strerror(errno));
+	check(g->sizes_host && g->status_host, "malloc: %s", strerror(errno));
 	return 0;
 error:
 	bufs_free(g);
