@@ -123,6 +123,38 @@ struct TiParams {
 	const uint32_t *T0;
 };
 
+// 16 keystream bytes per lane, 512 consecutive bytes per warp, to p (4-byte aligned; p + sh is
+// 16-byte aligned, sh uniform): one aligned 16-byte store per lane assembled with the low words
+// of the next lane's block; the first lane's head and the last lane's tail go out as words
+__device__ __forceinline__ void ti_store_row(char *p, const uint32_t s[4], uint32_t sh, uint32_t lane) {
+	if(sh == 0) {
+		__stcs(reinterpret_cast<uint4 *>(p), make_uint4(s[0], s[1], s[2], s[3]));
+		return;
+	}
+	const uint32_t ws = sh >> 2;   // 1..3 words
+	uint32_t nx[3];
+#pragma unroll
+	for(int i = 0; i < 3; i++) nx[i] = __shfl_down_sync(0xffffffffu, s[i], 1);
+	uint32_t c[4];
+#pragma unroll
+	for(int i = 0; i < 4; i++) {
+		uint32_t v = 0;
+#pragma unroll
+		for(int z = 0; z < 7; z++) if(i + ws == (uint32_t) z) v = z < 4 ? s[z & 3] : nx[z - 4 < 3 ? z - 4 : 2];
+		c[i] = v;
+	}
+	uint32_t *q = reinterpret_cast<uint32_t *>(p);
+	if(lane < 31) __stcs(reinterpret_cast<uint4 *>(p + sh), make_uint4(c[0], c[1], c[2], c[3]));
+	else {
+#pragma unroll
+		for(int i = 1; i < 4; i++) if((uint32_t) i >= ws) q[i] = s[i];
+	}
+	if(lane == 0) {
+#pragma unroll
+		for(int i = 0; i < 3; i++) if((uint32_t) i < ws) q[i] = s[i];
+	}
+}
+
 template <typename W, bool ALIGNED>
 __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P) {
 	extern __shared__ __align__(256) uint8_t smem[];
@@ -155,6 +187,8 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 			// units are the 256-aligned block groups of the x stream that overlap the shard's mask
 			const uint64_t B = (b_first & ~(uint64_t) 255) + (uint64_t) uu * (32 * TI_U) + i * 32 + lane;
 			const int64_t o = (int64_t) (B << 4) - (int64_t) X0; // byte offset of this block in the shard's mask
+			// uniform over the warp: all 32 blocks lie inside the shard's mask (voted before any lane drops out)
+			const bool full = __all_sync(0xffffffffu, o >= 0 && o + 16 <= (int64_t) nbytes);
 			if(o <= -16 || o >= (int64_t) nbytes) continue;      // before the start / past the end
 			uint32_t xs[4] = {0, 0, 0, 0}, ys[4] = {0, 0, 0, 0};
 			if(need_x) aes_ctr_block_g(P.key, lb, B, gx, xs);
@@ -177,6 +211,20 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 						ys[c] = v;
 					}
 				}
+			}
+			// the warp's 32 blocks are 512 consecutive mask bytes: when all of them lie inside the shard
+			// they leave as aligned 16-byte stores (full sectors), whatever the phase of the mask in
+			// the stream (blocks of an odd pair start 8 bytes into a 16-byte line)
+			if(full) {
+#pragma unroll
+				for(int e = 0; e < EPB; e++) {
+					if(w == 8) dot += (((uint64_t) xs[2 * e + 1] << 32) | xs[2 * e]) * (((uint64_t) ys[2 * e + 1] << 32) | ys[2 * e]);
+					else dot += (uint64_t) xs[e] * (uint64_t) ys[e];
+				}
+				const uint32_t sh = (16u - ((uint32_t) o & 15u)) & 15u;   // uniform: bytes to the next 16-byte line
+				if(xo) ti_store_row(reinterpret_cast<char *>(xo) + o, xs, sh, lane);
+				if(yo) ti_store_row(reinterpret_cast<char *>(yo) + o, ys, sh, lane);
+				continue;
 			}
 #pragma unroll
 			for(int e = 0; e < EPB; e++) {
