@@ -210,6 +210,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (p1_ctx_set_option), repeatable")
+    ap.add_argument("--wire-sample", type=int, default=3300, help="cross pairs to time with GPU (de)serialisation of every message (0 = skip)")
     ap.add_argument("--ot-sample", type=int, default=2, help="inner products of the --use_ot path to time (0 = skip)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -417,6 +418,23 @@ def main():
         e2e = {"value": macs / (ms_e2e * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
 
+    # ---- the same protocol with every message through the protobuf wire format on the GPU (what separate
+    # boxes execute per pair, minus the network): a bounded sample of the cross pairs, extrapolated
+    wire = None
+    if args.wire_sample > 0 and C:
+        npairs = min(C, args.wire_sample)
+
+        def wire_step(w):
+            box.cross_pairs_masking(key, seeded=seeded, wire=w, max_pairs=npairs)
+            box.sync()
+        wire_step(True)
+        ms_w, _ = timed(lambda: wire_step(True), 1)
+        ms_p, _ = timed(lambda: wire_step(False), 1)
+        wire = {"pairs": npairs, "ms_with_wire": ms_w, "ms_plain": ms_p, "us_per_pair_with_wire": ms_w * 1e3 / npairs,
+                "us_per_pair_plain": ms_p * 1e3 / npairs, "all_cross_pairs_ms_extrapolated": ms_w / npairs * C,
+                "messages_per_pair": 4, "note": "p1_msg_pack + p1_msg_unpack around each of the 4 messages of a pair "
+                "(src/phase1.c:100-145); the headline step hands messages over on the device"}
+
     # ---- --use_ot aggregation (BASELINE config 3 names it): a bounded sample of inner products over this
     # rank's rows through the correlated-OT kernels, reported as COT/s with the extrapolation to all cross pairs
     ot = None
@@ -481,7 +499,7 @@ def main():
                 "ring_macs_per_step": macs, "share_time_ms": ms_step, "wall_ms_per_step": ms_wall,
                 "gram_p1_equiv_macs": macs_gram_p1,
                 "gpu_launches": int(launches) * world, "kernels": kernels, "roofline": roofline, "clocks": clocks,
-                "e2e": e2e, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
+                "e2e": e2e, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
         print(json.dumps(line))
     if group is not None:
         dist.destroy_process_group()

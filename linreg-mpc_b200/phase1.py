@@ -232,15 +232,39 @@ class Phase1Box:
         self.bufs = [[t.empty(words, dtype=dt, device=self.dev) for _ in range(4)] for _ in self.ctxs]
         t.cuda.current_stream(self.dev).synchronize()
 
-    def cross_pairs_masking(self, ti_key, seeded=False):
+    def _ensure_wire(self):
+        if getattr(self, "wire", None) is not None:
+            return
+        t = self.torch
+        self.wire_stride = int(self.lib.p1_msg_max_bytes(self.ctxs[0], self.n_rows))
+        mk = lambda dt, k: t.zeros(k, dtype=dt, device=self.dev)
+        self.wire = [dict(buf=t.empty(self.batch_pairs * self.wire_stride, dtype=t.uint8, device=self.dev),
+                          sizes=mk(t.int64, self.batch_pairs), vals=mk(t.int64, self.batch_pairs),
+                          zero=mk(t.int64, self.batch_pairs), status=mk(t.int32, self.batch_pairs)) for _ in self.ctxs]
+        t.cuda.current_stream(self.dev).synchronize()
+
+    def _over_the_wire(self, ctx, pipe, vec, B):
+        """what a message costs between two boxes, minus the network: serialised by the sender
+        (send_pmsg, src/phase1.c:131-141) and parsed by the receiver (recv_pmsg, :111) in place"""
+        L, wr = self.lib, self.wire[pipe]
+        L.check(L.p1_msg_pack(ctx, vec, self.ld, self.n_rows, B, ptr(wr["zero"]), ptr(wr["buf"]), self.wire_stride, ptr(wr["sizes"])))
+        L.check(L.p1_msg_unpack(ctx, ptr(wr["buf"]), self.wire_stride, ptr(wr["sizes"]), B, self.n_rows, vec, self.ld,
+                                ptr(wr["vals"]), ptr(wr["status"])))
+
+    def cross_pairs_masking(self, ti_key, seeded=False, wire=False, max_pairs=None):
         """TI masking protocol for every cross pair (src/phase1.c:257-285 and :148-236).
         seeded=False: the TI materialises x and y once (what the reference ships);
         seeded=True : the TI computes only the values; each provider expands its own
-                      mask from (key, q) - same share words."""
-        C = self.sched.num_cross
+                      mask from (key, q) - same share words.
+        wire=True   : every one of the four messages of a pair additionally goes through the
+                      protobuf wire format on the GPU (pack by the sender, unpack by the receiver),
+                      as between separate boxes; the share words do not change."""
+        C = self.sched.num_cross if max_pairs is None else min(self.sched.num_cross, int(max_pairs))
         if not C:
             return
         self._ensure_bufs()
+        if wire:
+            self._ensure_wire()
         L = self.lib
         self._fan_out()
         for b, q0 in enumerate(range(0, C, self.batch_pairs)):
@@ -262,8 +286,15 @@ class Phase1Box:
                 L.check(L.p1_ti_generate(ctx, *args, None, None, self.ld, xy, r))      # TI: values only
                 L.check(L.p1_ti_generate(ctx, *args, xb, None, self.ld, None, None))   # party b expands x
                 L.check(L.p1_ti_generate(ctx, *args, None, yb, self.ld, None, None))   # party a expands y
+            if wire:
+                self._over_the_wire(ctx, pipe, xb, B)      # TI -> b
+                self._over_the_wire(ctx, pipe, yb, B)      # TI -> a
             L.check(L.p1_party_b_mask(ctx, self.data, cb, B, xb, self.ld, mb, self.ld))
+            if wire:
+                self._over_the_wire(ctx, pipe, mb, B)      # b -> a
             L.check(L.p1_party_a_step(ctx, self.data, ca, sa, B, yb, self.ld, mb, self.ld, ma, self.ld, acc))
+            if wire:
+                self._over_the_wire(ctx, pipe, ma, B)      # a -> b
             L.check(L.p1_party_b_share(ctx, self.data, cb, sb, B, ma, self.ld, acc))
         self._fan_in()
 
@@ -379,12 +410,12 @@ class Phase1Box:
         self.all_reduce()
         return self.finalize()
 
-    def run_masking(self, X, y, ti_key, seeded=False):
+    def run_masking(self, X, y, ti_key, seeded=False, wire=False):
         """whole phase 1 with the TI masking protocol; returns every provider's shares"""
         self.reset()
         self.encode(X, y)
         self.local_blocks()
-        self.cross_pairs_masking(ti_key, seeded=seeded)
+        self.cross_pairs_masking(ti_key, seeded=seeded, wire=wire)
         self.all_reduce()
         self.apply_values()
         return self.finalize()

@@ -401,6 +401,9 @@ def test_whole_phase1_random_instance(p1lib, oracle, b1, b2, prec, prec2):
     got = box.run_masking(X, y, po.TI_KEY)
     assert np.array_equal(got, want)
     assert box.launches() > 0
+    # same run with every message serialised and parsed on the GPU, and with provider-expanded masks
+    assert np.array_equal(box.run_masking(X, y, po.TI_KEY, wire=True), want)
+    assert np.array_equal(box.run_masking(X, y, po.TI_KEY, seeded=True), want)
     box.close()
 
 
