@@ -231,7 +231,11 @@ def main():
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version / debug lines stay off stdout: ONE JSON line there
+        # ONE JSON line on stdout: NCCL prints its version banner there at NCCL_DEBUG=VERSION (the redirect
+        # below only applies above that level), so that level is lowered; INFO/TRACE output goes to stderr
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
 
@@ -263,7 +267,7 @@ def main():
     torch.cuda.synchronize()
 
     gram = {"auto": pkg.ffi.P1_GRAM_AUTO, "imad": pkg.ffi.P1_GRAM_IMAD, "tcgen05": pkg.ffi.P1_GRAM_TCGEN05}[args.gram]
-    batch = args.batch_pairs or max(1, min(64, (256 << 20) // max(1, n_rows * w)))
+    batch = args.batch_pairs or max(1, min(256, (256 << 20) // max(1, n_rows * w)))   # ~256 MB of masks per vector buffer
     box = Phase1Box(lib, n, d, cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
                     row0=row0, n_rows=n_rows, batch_pairs=batch, pipes=args.pipes, gram_algo=gram, group=group)
     for o in args.opt:

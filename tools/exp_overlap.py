@@ -54,7 +54,7 @@ def loop(box, key, mode, frac=0.25):
 
 def main():
     lib = pkg.P1Lib()
-    n, d, p = 1_000_000, 500, 5
+    n, d, p = int(os.environ.get("N", "1000000")), 500, 5
     dev = torch.device("cuda", 0)
     g = torch.Generator(device=dev); g.manual_seed(1)
     X = torch.randn((n, d), dtype=torch.float64, device=dev, generator=g)
