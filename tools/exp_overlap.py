@@ -64,9 +64,14 @@ def main():
     pipes = int(os.environ.get("PIPES", "2"))
     batch = int(os.environ.get("BATCH", "33"))
     box = Phase1Box(lib, n, d, [k * (d // p) for k in range(p)], 56, batch_pairs=batch, pipes=pipes)
+    for o in os.environ.get("OPTS", "").split(","):
+        if o:
+            k, v = o.split("=")
+            for c in box.ctxs:
+                lib.check(lib.p1_ctx_set_option(c, k.encode(), int(v)))
     box.reset(); box.encode(X, y); box.sync()
     key = bytes(range(16))
-    out = {"pipes": pipes, "batch": batch}
+    out = {"pipes": pipes, "batch": batch, "opts": os.environ.get("OPTS", "")}
     for mode in ("full", "ti_novec", "ti_only", "party_only", "full"):
         loop(box, key, mode, 0.02)
         t0 = time.perf_counter()
