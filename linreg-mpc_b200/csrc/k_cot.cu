@@ -157,7 +157,6 @@ __global__ void __launch_bounds__(256) k_cot_finish(const W *__restrict__ pads, 
 
 // ------------------------------------------------------------------ host
 
-#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
 static int cot_new(p1_ctx *ctx, int role, const uint8_t (*seeds_a)[16], const uint8_t (*seeds_b)[16], const uint8_t *delta, p1_cot **out) {
 	P1_CHECK(out, "null output");

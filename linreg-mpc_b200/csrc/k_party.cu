@@ -119,7 +119,6 @@ static int launch_party(p1_ctx *ctx, const p1_data *data, const int32_t *cols, c
 	return 0;
 }
 
-#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
 extern "C" int p1_party_b_mask(p1_ctx *ctx, const p1_data *data, const int32_t *cols, size_t count,
 	const void *T_dev, size_t ld_T, void *out_dev, size_t ld_out) {

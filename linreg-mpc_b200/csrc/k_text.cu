@@ -18,7 +18,6 @@
 #define TX_MAXTOK 256                    // longest token converted on the device
 #define TX_SCAN_PER 4096                 // tile counts per CTA of the scan kernels (256 threads x 16)
 
-#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
 __device__ static const ulonglong2 pow5_tab[651] = {
 #include "pow5_table.inc"
@@ -117,36 +116,13 @@ __global__ void __launch_bounds__(TX_THREADS) k_tok_count(const TextParams P) {
 	}
 }
 
-// exclusive scan of one value per thread over the 256-thread CTA
-__device__ __forceinline__ uint32_t tx_block_scan(uint32_t v, uint32_t *s_warp, uint32_t *total) {
-	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	uint32_t inc = v;
-#pragma unroll
-	for(int o = 1; o < 32; o <<= 1) {
-		const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-		if(lane >= (uint32_t) o) inc += t;
-	}
-	if(lane == 31) s_warp[wid] = inc;
-	__syncthreads();
-	if(threadIdx.x == 0) {
-		uint32_t run = 0;
-		for(int i = 0; i < TX_THREADS / 32; i++) { const uint32_t c = s_warp[i]; s_warp[i] = run; run += c; }
-		s_warp[TX_THREADS / 32] = run;
-	}
-	__syncthreads();
-	const uint32_t r = s_warp[wid] + inc - v;
-	*total = s_warp[TX_THREADS / 32];
-	__syncthreads();
-	return r;
-}
-
 __global__ void __launch_bounds__(TX_THREADS) k_tok_scan1(const TextParams P) {
 	__shared__ uint32_t s_warp[TX_THREADS / 32 + 1];
 	const uint64_t first = (uint64_t) blockIdx.x * TX_SCAN_PER + threadIdx.x * 16;
 	uint32_t sum = 0;
 	for(int e = 0; e < 16; e++) if(first + e < P.tiles) sum += P.tile_cnt[first + e];
 	uint32_t total;
-	tx_block_scan(sum, s_warp, &total);
+	p1_block_excl_scan256(sum, s_warp, &total);
 	if(threadIdx.x == 0) P.part[blockIdx.x] = total;
 }
 
@@ -163,7 +139,7 @@ __global__ void __launch_bounds__(TX_THREADS) k_tok_scan3(const TextParams P) {
 	uint32_t c[16], sum = 0;
 	for(int e = 0; e < 16; e++) { c[e] = first + e < P.tiles ? P.tile_cnt[first + e] : 0; sum += c[e]; }
 	uint32_t total;
-	uint64_t run = P.part[blockIdx.x] + tx_block_scan(sum, s_warp, &total);
+	uint64_t run = P.part[blockIdx.x] + p1_block_excl_scan256(sum, s_warp, &total);
 	for(int e = 0; e < 16; e++) if(first + e < P.tiles) { P.tile_off[first + e] = run; run += c[e]; }
 }
 
@@ -225,7 +201,7 @@ __global__ void __launch_bounds__(TX_THREADS) k_tok_parse(const TextParams P) {
 	const uint32_t prev = (t0 == 0 && threadIdx.x == 0) ? 1u : (tx_is_space(sb[lb - 1]) ? 1u : 0u);
 	const uint32_t starts = ~sp & ((sp << 1) | prev);
 	uint32_t total;
-	uint64_t k = P.tile_off[blockIdx.x] + tx_block_scan(__popc(starts), s_warp, &total);
+	uint64_t k = P.tile_off[blockIdx.x] + p1_block_excl_scan256(__popc(starts), s_warp, &total);
 	for(uint32_t s = starts; s; s &= s - 1, k++) {
 		const uint32_t i = __ffs(s) - 1;
 		double v;

@@ -17,7 +17,6 @@
 #define UP_BPT 32                         // bytes per thread
 #define UP_TILE (WR_THREADS * UP_BPT)     // bytes per tile
 
-#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
 // ------------------------------------------------------------------ device helpers
 
@@ -27,49 +26,25 @@ __device__ __forceinline__ uint32_t vi_len64(uint64_t v) {
 	return (bits + 6) / 7;
 }
 
-// the low 56 bits of v as eight 7-bit groups, one per byte
-__device__ __forceinline__ uint64_t vi_spread56(uint64_t v) {
-	uint64_t x = v & 0x00ffffffffffffffull;
-	x = (x & 0x000000000fffffffull) | ((x & 0x00fffffff0000000ull) << 4);
-	x = (x & 0x00003fff00003fffull) | ((x & 0x0fffc0000fffc000ull) << 2);
-	x = (x & 0x007f007f007f007full) | ((x & 0x3f803f803f803f80ull) << 1);
-	return x;
+// 28 bits -> four bytes of 7 bits each (two mask-and-shift steps on a 32-bit word) and back
+__device__ __forceinline__ uint32_t vi_spread28(uint32_t t) {
+	const uint32_t x = (t & 0x00003fffu) | ((t << 2) & 0x3fff0000u);
+	return (x & 0x007f007fu) | ((x << 1) & 0x7f007f00u);
 }
-// inverse: eight bytes with 7 payload bits each -> 56 bits
-__device__ __forceinline__ uint64_t vi_gather56(uint64_t y) {
-	y &= 0x7f7f7f7f7f7f7f7full;
-	y = ((y & 0x7f007f007f007f00ull) >> 1) | (y & 0x007f007f007f007full);
-	y = ((y & 0x3fff00003fff0000ull) >> 2) | (y & 0x00003fff00003fffull);
-	y = ((y & 0x0fffffff00000000ull) >> 4) | (y & 0x000000000fffffffull);
-	return y;
+__device__ __forceinline__ uint32_t vi_gather28(uint32_t y) {
+	y = (y & 0x007f007fu) | ((y & 0x7f007f00u) >> 1);
+	return (y & 0x00003fffu) | ((y & 0x3fff0000u) >> 2);
 }
-
-// exclusive scan of one value per thread over the CTA; *total = sum over the CTA
-__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *s_warp, uint32_t *total) {
-	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	uint32_t inc = v;
-#pragma unroll
-	for(int o = 1; o < 32; o <<= 1) {
-		const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-		if(lane >= (uint32_t) o) inc += t;
-	}
-	if(lane == 31) s_warp[wid] = inc;
-	__syncthreads();
-	if(wid == 0) {
-		uint32_t w = lane < (WR_THREADS / 32) ? s_warp[lane] : 0, wi = w;
-#pragma unroll
-		for(int o = 1; o < 32; o <<= 1) {
-			const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-			if(lane >= (uint32_t) o) wi += t;
-		}
-		if(lane < (WR_THREADS / 32)) s_warp[lane] = wi - w;
-		if(lane == 31) s_warp[WR_THREADS / 32] = wi;
-	}
-	__syncthreads();
-	const uint32_t r = s_warp[wid] + inc - v;
-	*total = s_warp[WR_THREADS / 32];
-	__syncthreads();   // s_warp may be reused
-	return r;
+// 0x80 in the lowest min(c, 4) bytes
+__device__ __forceinline__ uint32_t vi_cont4(uint32_t c) {
+	return c ? 0x80808080u >> (8 * (4 - min(c, 4u))) : 0u;
+}
+// the varint of v (L bytes) as three little-endian words: bytes 0-3, 4-7, 8-9; zero beyond byte L-1
+__device__ __forceinline__ void vi_encode(uint64_t v, uint32_t L, uint32_t w[3]) {
+	const uint32_t lo = (uint32_t) v, hi = (uint32_t) (v >> 32), c = L - 1, t2 = hi >> 24;
+	w[0] = vi_spread28(lo & 0x0fffffffu) | vi_cont4(c);
+	w[1] = vi_spread28(__funnelshift_r(lo, hi, 28) & 0x0fffffffu) | vi_cont4(c > 4 ? c - 4 : 0);
+	w[2] = (t2 & 0x7fu) | ((t2 & 0x80u) << 1) | (c > 8 ? 0x80u : 0u);
 }
 
 // the thread's PK_WPT consecutive words of message p, zero past n (vector loads: rows are
@@ -199,15 +174,16 @@ __global__ void __launch_bounds__(WR_THREADS) k_pack_write(const PackParams P) {
 		tot += len[e];
 	}
 	uint32_t tile_bytes;
-	const uint32_t excl = block_excl_scan(tot, s_warp, &tile_bytes);
+	const uint32_t excl = p1_block_excl_scan256(tot, s_warp, &tile_bytes);
 	const uint64_t goff = P.tile_off[(uint64_t) p * P.tiles + tile];
 	const uint32_t gshift = (uint32_t) goff & 15u;
 	uint8_t *sb = reinterpret_cast<uint8_t *>(stage);
 
+	// the thread's varints are appended to a word-aligned stream: `carry` holds the `fill` (0..3)
+	// bytes not yet written, every varint contributes up to three words through funnel shifts
 	const uint32_t pos = gshift + excl, head = pos & 3u;
-	uint32_t wi = pos >> 2, fill = head;
-	bool partial = head != 0;
-	uint64_t acc = 0;
+	uint32_t wi = pos >> 2, fill = head, carry = 0;
+	bool partial = head != 0;      // the first word is shared with the previous thread: byte stores
 	auto emit = [&](uint32_t word) {
 		if(partial) {
 			for(uint32_t b = head; b < 4; b++) sb[wi * 4 + b] = (uint8_t) (word >> (8 * b));
@@ -215,30 +191,23 @@ __global__ void __launch_bounds__(WR_THREADS) k_pack_write(const PackParams P) {
 		} else stage[wi] = word;
 		wi++;
 	};
-	auto append = [&](uint64_t b, uint32_t k) {
-		uint64_t carry = fill ? b >> (64 - 8 * fill) : 0;
-		acc |= b << (8 * fill);
-		fill += k;
-		while(fill >= 4) {
-			emit((uint32_t) acc);
-			acc = (acc >> 32) | (carry << 32);
-			carry = 0;
-			fill -= 4;
-		}
-	};
 #pragma unroll
 	for(int e = 0; e < PK_WPT; e++) {
 		const uint32_t L = len[e];
 		if(!L) continue;
-		const uint32_t c = min(L - 1, 8u);
-		const uint64_t cont = c ? 0x8080808080808080ull >> (8 * (8 - c)) : 0;
-		append(vi_spread56(v[e]) | cont, min(L, 8u));
-		if(MAXLEN > 8 && L > 8) {
-			const uint64_t hi = ((v[e] >> 56) & 0x7f) | (L == 10 ? 0x80 : 0) | ((v[e] >> 63) << 8);
-			append(hi, L - 8);
-		}
+		uint32_t w[3];
+		vi_encode(v[e], L, w);
+		const uint32_t sh = 8 * fill;
+		const uint32_t e0 = carry | (w[0] << sh), e1 = __funnelshift_l(w[0], w[1], sh),
+			e2 = __funnelshift_l(w[1], w[2], sh), e3 = __funnelshift_l(w[2], 0u, sh);
+		const uint32_t total = fill + L, nw = total >> 2;      // nw <= 3
+		if(nw > 0) emit(e0);
+		if(nw > 1) emit(e1);
+		if(nw > 2) emit(e2);
+		carry = nw == 0 ? e0 : nw == 1 ? e1 : nw == 2 ? e2 : e3;
+		fill = total & 3u;
 	}
-	for(uint32_t b = partial ? head : 0; b < fill; b++) sb[wi * 4 + b] = (uint8_t) (acc >> (8 * b));
+	for(uint32_t b = partial ? head : 0; b < fill; b++) sb[wi * 4 + b] = (uint8_t) (carry >> (8 * b));
 	__syncthreads();
 
 	uint8_t *g = P.out + (uint64_t) p * P.stride + (goff - gshift);   // 16-byte aligned
@@ -293,9 +262,9 @@ __device__ __forceinline__ uint32_t up_term_mask(const uint4 a, const uint4 b) {
 	uint32_t m = 0;
 #pragma unroll
 	for(int i = 0; i < 8; i++) {
-		const uint32_t t = ~w[i] & 0x80808080u;            // 0x80 in every terminator byte
-		// gather bits 7, 15, 23, 31 into a nibble
-		const uint32_t nib = ((t >> 7) & 1u) | ((t >> 14) & 2u) | ((t >> 21) & 4u) | ((t >> 28) & 8u);
+		// 0x80 in every terminator byte; bits 7, 15, 23, 31 gathered into a nibble by one multiplication
+		// (the four partial products land on bits 21..24 and nothing else does)
+		const uint32_t nib = ((((~w[i] & 0x80808080u) >> 7) * 0x00204081u) >> 21) & 0xfu;
 		m |= nib << (4 * i);
 	}
 	return m;
@@ -328,7 +297,10 @@ __global__ void __launch_bounds__(WR_THREADS) k_unpack_count(const UnpackParams 
 	if(rm) {
 		const uint4 a = __ldg(reinterpret_cast<const uint4 *>(m + base));
 		const uint4 b = __ldg(reinterpret_cast<const uint4 *>(m + base + 16));
-		cnt = __popc(up_term_mask(a, b) & rm);
+		if(rm == 0xffffffffu) {
+			cnt = __popc(~a.x & 0x80808080u) + __popc(~a.y & 0x80808080u) + __popc(~a.z & 0x80808080u) + __popc(~a.w & 0x80808080u)
+				+ __popc(~b.x & 0x80808080u) + __popc(~b.y & 0x80808080u) + __popc(~b.z & 0x80808080u) + __popc(~b.w & 0x80808080u);
+		} else cnt = __popc(up_term_mask(a, b) & rm);
 	}
 #pragma unroll
 	for(int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
@@ -425,7 +397,7 @@ __global__ void __launch_bounds__(WR_THREADS) k_unpack_write(const UnpackParams 
 	const uint32_t prev_term = !(sb[lb - 1] & 0x80);   // the byte before pay_start is the last byte of the length varint
 	const uint32_t starts = ((term << 1) | prev_term) & rm;
 	uint32_t tile_total;
-	const uint32_t before = block_excl_scan(__popc(term & rm), s_warp, &tile_total);
+	const uint32_t before = p1_block_excl_scan256(__popc(term & rm), s_warp, &tile_total);
 	uint64_t index = P.tile_off[(uint64_t) p * P.tiles + tile] + before;
 	W *out = (W *) P.vec + (uint64_t) p * P.ld;
 	uint32_t bad = 0;
@@ -437,17 +409,17 @@ __global__ void __launch_bounds__(WR_THREADS) k_unpack_write(const UnpackParams 
 		const uint32_t *wp = reinterpret_cast<const uint32_t *>(sb + (o & ~3u));
 		const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
 		const uint32_t d0 = __funnelshift_r(w0, w1, sh), d1 = __funnelshift_r(w1, w2, sh), d2 = __funnelshift_r(w2, w3, sh);
-		const uint64_t lo8 = ((uint64_t) d1 << 32) | d0;
-		const uint64_t tm = ~lo8 & 0x8080808080808080ull;
-		uint64_t v = vi_gather56(lo8);
-		if(tm) {
-			const uint32_t len = (uint32_t) (__ffsll((long long) tm) >> 3);    // 1..8
-			if(len < 8) v &= (1ull << (7 * len)) - 1;
-		} else if(!(d2 & 0x80u)) {
-			v |= (uint64_t) (d2 & 0x7fu) << 56;
-		} else if(!(d2 & 0x8000u)) {
-			v |= ((uint64_t) (d2 & 0x7fu) << 56) | ((uint64_t) ((d2 >> 8) & 1u) << 63);
-		} else bad = 1;
+		// all ten candidate bytes decoded, then cut at the first terminator
+		uint64_t v = (uint64_t) vi_gather28(d0 & 0x7f7f7f7fu) | ((uint64_t) vi_gather28(d1 & 0x7f7f7f7fu) << 28)
+			| ((uint64_t) (d2 & 0x7fu) << 56) | ((uint64_t) ((d2 >> 8) & 1u) << 63);
+		const uint32_t t0m = ~d0 & 0x80808080u, t1m = ~d1 & 0x80808080u;
+		uint32_t len;
+		if(t0m) len = __ffs(t0m) >> 3;
+		else if(t1m) len = 4 + (__ffs(t1m) >> 3);
+		else if(!(d2 & 0x80u)) len = 9;
+		else if(!(d2 & 0x8000u)) len = 10;
+		else { len = 10; bad = 1; }
+		if(len < 10) v &= (1ull << (7 * len)) - 1;
 		if(k < P.n) out[k] = (W) v;
 	}
 	if(bad) atomicOr(P.status + p, P1_MSG_BAD_VARINT);

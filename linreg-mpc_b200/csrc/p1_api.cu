@@ -111,7 +111,6 @@ extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 	delete ctx;
 }
 
-#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
 extern "C" int p1_ctx_sync(p1_ctx *ctx) {
 	P1_ENTER(ctx);

@@ -63,6 +63,9 @@ int p1_fail(const char *fmt, ...);
 #define P1_LAUNCHED(ctx) do { (ctx)->launches++; p1_prof_end(ctx); cudaError_t e_ = cudaGetLastError(); if(e_ != cudaSuccess) \
 	return p1_fail("%s:%d: kernel launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); } while(0)
 
+// every entry point: context checked, calls on one context serialised, device selected
+#define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
+
 static inline size_t p1_round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
 static inline size_t p1_nA(size_t d) { return d * (d + 1) / 2; }
 
@@ -94,5 +97,28 @@ __device__ __forceinline__ uint64_t p1_warp_sum(uint64_t v) {
 }
 __device__ __forceinline__ void p1_red_add(uint64_t *p, uint64_t v) {
 	atomicAdd(reinterpret_cast<unsigned long long *>(p), static_cast<unsigned long long>(v));
+}
+// exclusive scan of one 32-bit value per thread over a 256-thread CTA (s_warp: 9 words of shared
+// memory); *total = sum over the CTA.  Ends with a barrier, so s_warp may be reused at once.
+__device__ __forceinline__ uint32_t p1_block_excl_scan256(uint32_t v, uint32_t *s_warp, uint32_t *total) {
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for(int o = 1; o < 32; o <<= 1) {
+		const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+		if(lane >= (uint32_t) o) inc += t;
+	}
+	if(lane == 31) s_warp[wid] = inc;
+	__syncthreads();
+	if(threadIdx.x == 0) {
+		uint32_t run = 0;
+		for(int i = 0; i < 8; i++) { const uint32_t c = s_warp[i]; s_warp[i] = run; run += c; }
+		s_warp[8] = run;
+	}
+	__syncthreads();
+	const uint32_t r = s_warp[wid] + inc - v;
+	*total = s_warp[8];
+	__syncthreads();
+	return r;
 }
 #endif
