@@ -231,8 +231,9 @@ extern "C" int p1_parse_doubles(p1_ctx *ctx, const char *text, size_t bytes, dou
 	size_t o_text = 0, o_off = o_text + (on_dev ? 0 : p1_round_up(bytes, 256));
 	size_t o_part = o_off + tiles * 8, o_cnt = o_part + nparts * 8, o_def = o_cnt + 16, o_tc = o_def + cap * 8;
 	const size_t total = o_tc + tiles * 4;
-	char *ws = NULL;
-	P1_CUDA(cudaMallocAsync((void **) &ws, total, ctx->stream));
+	p1_tmp tmp;
+	P1_CUDA(tmp.alloc(total, ctx->stream));
+	char *ws = (char *) tmp.p;
 	TextParams P;
 	P.text = (const uint8_t *) text;
 	if(!on_dev) {
@@ -262,6 +263,5 @@ extern "C" int p1_parse_doubles(p1_ctx *ctx, const char *text, size_t bytes, dou
 		P1_CUDA(cudaMemcpy(deferred, P.deferred, got * 8, cudaMemcpyDeviceToHost));
 		std::sort(deferred, deferred + got);
 	}
-	P1_CUDA(cudaFreeAsync(ws, ctx->stream));
 	return 0;
 }

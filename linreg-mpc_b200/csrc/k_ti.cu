@@ -123,35 +123,37 @@ struct TiParams {
 	const uint32_t *T0;
 };
 
-// 16 keystream bytes per lane, 512 consecutive bytes per warp, to p (4-byte aligned; p + sh is
-// 16-byte aligned, sh uniform): one aligned 16-byte store per lane assembled with the low words
-// of the next lane's block; the first lane's head and the last lane's tail go out as words
-__device__ __forceinline__ void ti_store_row(char *p, const uint32_t s[4], uint32_t sh, uint32_t lane) {
-	if(sh == 0) {
+// 16 keystream bytes per lane, 512 consecutive bytes per warp, to p (4-byte aligned; p + 4*WS is
+// 16-byte aligned): one aligned 16-byte store per lane assembled with the low WS words of the
+// next lane's block; the first lane's head and the last lane's tail go out as words.  WS is a
+// template constant so that the word selection costs no instructions.
+template <int WS>
+__device__ __forceinline__ void ti_store_row_ws(char *p, const uint32_t s[4], uint32_t lane) {
+	if(WS == 0) {
 		__stcs(reinterpret_cast<uint4 *>(p), make_uint4(s[0], s[1], s[2], s[3]));
 		return;
 	}
-	const uint32_t ws = sh >> 2;   // 1..3 words
-	uint32_t nx[3];
-#pragma unroll
-	for(int i = 0; i < 3; i++) nx[i] = __shfl_down_sync(0xffffffffu, s[i], 1);
 	uint32_t c[4];
 #pragma unroll
-	for(int i = 0; i < 4; i++) {
-		uint32_t v = 0;
-#pragma unroll
-		for(int z = 0; z < 7; z++) if(i + ws == (uint32_t) z) v = z < 4 ? s[z & 3] : nx[z - 4 < 3 ? z - 4 : 2];
-		c[i] = v;
-	}
+	for(int i = 0; i < 4; i++) c[i] = i + WS < 4 ? s[(i + WS) & 3] : __shfl_down_sync(0xffffffffu, s[(i + WS) & 3], 1);
 	uint32_t *q = reinterpret_cast<uint32_t *>(p);
-	if(lane < 31) __stcs(reinterpret_cast<uint4 *>(p + sh), make_uint4(c[0], c[1], c[2], c[3]));
+	if(lane < 31) __stcs(reinterpret_cast<uint4 *>(p + 4 * WS), make_uint4(c[0], c[1], c[2], c[3]));
 	else {
 #pragma unroll
-		for(int i = 1; i < 4; i++) if((uint32_t) i >= ws) q[i] = s[i];
+		for(int i = WS; i < 4; i++) q[i] = s[i];
 	}
 	if(lane == 0) {
 #pragma unroll
-		for(int i = 0; i < 3; i++) if((uint32_t) i < ws) q[i] = s[i];
+		for(int i = 0; i < WS; i++) q[i] = s[i];
+	}
+}
+// sh = bytes from p to the next 16-byte line, uniform over the warp
+__device__ __forceinline__ void ti_store_row(char *p, const uint32_t s[4], uint32_t sh, uint32_t lane) {
+	switch(sh >> 2) {
+	case 0: ti_store_row_ws<0>(p, s, lane); break;
+	case 1: ti_store_row_ws<1>(p, s, lane); break;
+	case 2: ti_store_row_ws<2>(p, s, lane); break;
+	default: ti_store_row_ws<3>(p, s, lane); break;
 	}
 }
 

@@ -545,9 +545,13 @@ extern "C" int p1_share_bits(p1_ctx *ctx, const void *shares, size_t n, uint8_t 
 	P1_CHECK(shares && sel, "p1_share_bits: arguments may not be null");
 	const size_t w = ctx->bits_p2 / 8, in_bytes = n * w, out_bytes = n * ctx->bits_p2;
 	const bool in_dev = p1_is_device_ptr(shares), out_dev = p1_is_device_ptr(sel);
+	p1_tmp scratch;
 	void *tmp = NULL;
 	const size_t tmp_bytes = (in_dev ? 0 : p1_round_up(in_bytes, 256)) + (out_dev ? 0 : out_bytes);
-	if(tmp_bytes) P1_CUDA(cudaMallocAsync(&tmp, tmp_bytes, ctx->stream));
+	if(tmp_bytes) {
+		P1_CUDA(scratch.alloc(tmp_bytes, ctx->stream));
+		tmp = scratch.p;
+	}
 	const void *src = shares;
 	uint8_t *dst = sel;
 	if(!in_dev) {
@@ -566,6 +570,5 @@ extern "C" int p1_share_bits(p1_ctx *ctx, const void *shares, size_t n, uint8_t 
 		P1_CUDA(cudaMemcpyAsync(sel, dst, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
 		P1_CUDA(cudaStreamSynchronize(ctx->stream));
 	}
-	if(tmp) P1_CUDA(cudaFreeAsync(tmp, ctx->stream));
 	return 0;
 }

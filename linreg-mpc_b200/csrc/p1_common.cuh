@@ -66,6 +66,14 @@ int p1_fail(const char *fmt, ...);
 // every entry point: context checked, calls on one context serialised, device selected
 #define P1_ENTER(ctx) P1_CHECK(ctx, "null context"); std::lock_guard<std::mutex> lock_((ctx)->mu); P1_CUDA(cudaSetDevice((ctx)->device))
 
+// stream-ordered temporary (cudaMallocAsync) released on every return path of an entry point
+struct p1_tmp {
+	void *p = nullptr;
+	cudaStream_t st = nullptr;
+	cudaError_t alloc(size_t bytes, cudaStream_t stream) { st = stream; return cudaMallocAsync(&p, bytes, stream); }
+	~p1_tmp() { if(p) cudaFreeAsync(p, st); }
+};
+
 static inline size_t p1_round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
 static inline size_t p1_nA(size_t d) { return d * (d + 1) / 2; }
 
