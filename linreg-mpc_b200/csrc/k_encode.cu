@@ -150,7 +150,9 @@ __device__ __forceinline__ void enc_cta(const SRC *__restrict__ src, size_t rows
 
 // grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8)
 template <typename W, typename SRC>
-__global__ void __launch_bounds__(256, 2) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
+// resident CTAs per SM: 3 with 4-byte words (80 registers, a few spills, +10 % measured), 2 with 8-byte words
+// (3 gained nothing there: 1.59 vs 1.58 ms)
+__global__ void __launch_bounds__(256, (sizeof(W) == 4 ? 3 : 2)) k_rows_to_cols(const SRC *__restrict__ src, size_t rows, size_t d, size_t row_off,
 	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep) {
 	__shared__ W tile[ENC_TILE_ROWS][33];
 	const bool full = (size_t) blockIdx.x * 32 + 32 <= d && (size_t) blockIdx.y * ENC_ROWS_PER_CTA + ENC_ROWS_PER_CTA <= rows;
