@@ -73,3 +73,14 @@ def test_run_party_large_vectors_sequential_diagonal(p1lib, tmp_path):
     po.write_instance(path, X, y, cs)
     (rs, _, _), (gs, _, _) = both(path, d, len(cs), 64, 64, 56, 0, False)
     assert np.array_equal(gs, rs)
+
+
+def test_run_party_medium_instance_default_batch(p1lib, tmp_path):
+    """four providers, runs longer than one message tile, default batching (whole runs per batch)"""
+    n, d, cs = 20000, 16, [0, 4, 8, 12]
+    X, y, _ = po.generate_lin_regression(n, d, seed=24)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, rsent), (gs, _, gsent) = both(path, d, len(cs), 64, 64, 56, 0, False)
+    assert np.array_equal(gs, rs)
+    assert np.array_equal(gsent, rsent)
