@@ -160,6 +160,152 @@ __global__ void __launch_bounds__(256, (sizeof(W) == 4 ? 3 : 2)) k_rows_to_cols(
 	else enc_cta<W, SRC, false>(src, rows, d, row_off, xt, ld, stats, ep, tile);
 }
 
+// ------------------------------------------------------------------ encode + digit planes
+//
+// Same pass as k_rows_to_cols, also writing the balanced base-256 digits of every word in the layout the
+// tcgen05 Gram reads through TMA (k_gram_tc.cu): planes[row/128][digit][column 0..d][row%128], Lg digits per
+// word.  That removes k_limb_split's re-read of the whole column store before every Gram.  A thread owns
+// 4 consecutive rows of a column here (one 16/32-byte word store, one packed 32-bit store per digit), so the
+// tile is read back along rows: the XOR swizzle keeps both the row-wise writes and these reads conflict-free.
+
+__device__ __forceinline__ int enc_swz(int r, int c) { return r * 32 + (c ^ ((r >> 2) & 31)); }
+
+template <typename W>
+__device__ __forceinline__ void enc_store4(W *dst, const W (&w)[4]) {
+	if(sizeof(W) == 8) {
+		*reinterpret_cast<ulonglong2 *>(dst) = make_ulonglong2((uint64_t) w[0], (uint64_t) w[1]);
+		*reinterpret_cast<ulonglong2 *>(dst + 2) = make_ulonglong2((uint64_t) w[2], (uint64_t) w[3]);
+	} else {
+		*reinterpret_cast<uint4 *>(dst) = make_uint4((uint32_t) w[0], (uint32_t) w[1], (uint32_t) w[2], (uint32_t) w[3]);
+	}
+}
+
+// digits of 4 words, digit l of all four packed into one 32-bit store at dst + l*stride
+template <typename W>
+__device__ __forceinline__ void enc_digits4(const W (&w)[4], uint8_t *dst, size_t stride, int Lg) {
+	typedef typename p1_word<W>::s S;
+	int64_t v[4];
+#pragma unroll
+	for(int i = 0; i < 4; i++) v[i] = (int64_t) (S) w[i];
+#pragma unroll
+	for(int l = 0; l < 4; l++) {
+		if(l < Lg) {
+			uint32_t packed = 0;
+#pragma unroll
+			for(int i = 0; i < 4; i++) {
+				const int64_t dg = (int64_t) (int8_t) (v[i] & 0xff);
+				v[i] = (v[i] - dg) >> 8;
+				packed |= ((uint32_t) dg & 0xffu) << (8 * i);
+			}
+			*reinterpret_cast<uint32_t *>(dst + (size_t) l * stride) = packed;
+		}
+	}
+}
+
+template <typename W, bool FULL>
+__device__ __forceinline__ void enc_cta_planes(const double *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, const EncodeParams &ep, W *tile, uint8_t *__restrict__ planes, int Lg) {
+	constexpr int NL = ENC_TILE_ROWS / 8;
+	constexpr int NSUB = ENC_ROWS_PER_CTA / ENC_TILE_ROWS;
+	const int tx = threadIdx.x, ty = threadIdx.y;
+	const size_t c0 = (size_t) blockIdx.x * 32;
+	const size_t rbase = (size_t) blockIdx.y * ENC_ROWS_PER_CTA;
+	const size_t c_in = c0 + tx;
+	ColStats cs[4];
+#pragma unroll
+	for(int u = 0; u < 4; u++) cs[u].init();
+	double v[NL];
+	const size_t step = 8 * d;
+	const double *ip = src + (rbase + ty) * d + c_in;
+	auto fetch = [&](size_t r0) {
+#pragma unroll
+		for(int u = 0; u < NL; u++) {
+			if(FULL) v[u] = __ldcs(ip);
+			else v[u] = (r0 + ty + 8 * u < rows && c_in < d) ? __ldcs(ip) : 0.0;
+			ip += step;
+		}
+	};
+	fetch(rbase);
+	const size_t pcol = (d + 1) * 128;                    // bytes between digits of a K-block
+	W *op = xt + (c0 + ty) * ld + row_off + rbase + 4 * tx;
+	uint8_t *pp = planes + ((row_off + rbase) / 128) * (size_t) Lg * pcol + (c0 + ty) * 128 + 4 * tx;
+#pragma unroll 1
+	for(int sub = 0; sub < NSUB; sub++) {
+		const size_t r0 = rbase + (size_t) sub * ENC_TILE_ROWS;
+		if(!FULL && r0 >= rows) break;
+#pragma unroll
+		for(int u = 0; u < NL; u++) {
+			const int rr = ty + 8 * u;
+			if(FULL) tile[enc_swz(rr, tx)] = load_word<W, double>(v[u], ep);
+			else tile[enc_swz(rr, tx)] = (r0 + rr < rows && c_in < d) ? load_word<W, double>(v[u], ep) : (W) 0;
+		}
+		__syncthreads();
+		if(sub + 1 < NSUB && (FULL || r0 + ENC_TILE_ROWS < rows)) fetch(r0 + ENC_TILE_ROWS);
+#pragma unroll
+		for(int u = 0; u < 4; u++) {
+			const int cc = ty + 8 * u;
+			if(FULL || (c0 + cc < d && r0 + 4 * tx < rows)) {
+				W w[4];
+#pragma unroll
+				for(int i = 0; i < 4; i++) w[i] = tile[(4 * tx + i) * 32 + (cc ^ tx)];       // enc_swz(4tx+i, cc)
+				W *dst = op + (size_t) (8 * u) * ld;
+				if(FULL || r0 + 4 * tx + 4 <= rows) {
+					enc_store4<W>(dst, w);
+#pragma unroll
+					for(int i = 0; i < 4; i++) cs[u].add<W>(w[i]);
+				} else {
+#pragma unroll
+					for(int i = 0; i < 4; i++) if(r0 + 4 * tx + i < rows) { dst[i] = w[i]; cs[u].add<W>(w[i]); }
+				}
+				enc_digits4<W>(w, pp + (size_t) (8 * u) * 128, pcol, Lg);
+			}
+		}
+		op += ENC_TILE_ROWS;
+		pp += (size_t) Lg * pcol;
+		__syncthreads();
+	}
+#pragma unroll
+	for(int u = 0; u < 4; u++) {
+		cs[u].warp_reduce();
+		const size_t c = c0 + ty + 8 * u;
+		if(tx == 0 && c < d) cs[u].flush(stats + 4 * c);
+	}
+}
+
+// grid (ceil(d/32), ceil(rows/ENC_ROWS_PER_CTA)), block (32,8); row_off must be a multiple of 128
+template <typename W>
+__global__ void __launch_bounds__(256, 2) k_rows_to_cols_planes(const double *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep, uint8_t *__restrict__ planes, int Lg) {
+	__shared__ __align__(16) W tile[ENC_TILE_ROWS * 32];
+	const bool full = (size_t) blockIdx.x * 32 + 32 <= d && (size_t) blockIdx.y * ENC_ROWS_PER_CTA + ENC_ROWS_PER_CTA <= rows;
+	if(full) enc_cta_planes<W, true>(src, rows, d, row_off, xt, ld, stats, ep, tile, planes, Lg);
+	else enc_cta_planes<W, false>(src, rows, d, row_off, xt, ld, stats, ep, tile, planes, Lg);
+}
+
+// target vector: a thread owns 4 consecutive rows; pl = the planes of column d
+template <typename W>
+__global__ void __launch_bounds__(256) k_vec_encode_planes(const double *__restrict__ src, size_t n, W *__restrict__ col,
+	uint64_t *__restrict__ stats, EncodeParams ep, uint8_t *__restrict__ pl, size_t pcol, int Lg) {
+	ColStats cs;
+	cs.init();
+	for(size_t r = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 4; r < n; r += (size_t) gridDim.x * blockDim.x * 4) {
+		W w[4];
+#pragma unroll
+		for(int i = 0; i < 4; i++) w[i] = r + i < n ? load_word<W, double>(src[r + i], ep) : (W) 0;
+		if(r + 4 <= n) {
+			enc_store4<W>(col + r, w);
+#pragma unroll
+			for(int i = 0; i < 4; i++) cs.add<W>(w[i]);
+		} else {
+#pragma unroll
+			for(int i = 0; i < 4; i++) if(r + i < n) { col[r + i] = w[i]; cs.add<W>(w[i]); }
+		}
+		enc_digits4<W>(w, pl + (r / 128) * (size_t) Lg * pcol + (r % 128), pcol, Lg);
+	}
+	cs.warp_reduce();
+	if((threadIdx.x & 31) == 0) cs.flush(stats);
+}
+
 template <typename W, typename SRC>
 __global__ void __launch_bounds__(256) k_vec_encode(const SRC *__restrict__ src, size_t n, W *__restrict__ col,
 	uint64_t *__restrict__ stats, EncodeParams ep) {
@@ -217,6 +363,27 @@ static int launch_vec(p1_ctx *ctx, const SRC *src, p1_data *out, EncodeParams ep
 int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
 	const double *y_dev, double normalizer, int precision, p1_data *out) {
 	EncodeParams ep = {normalizer, (double) (1ll << precision), ctx->bits_p2};
+	if(out->planes) {
+		// one pass that also writes the digit planes of the tensor-core Gram
+		P1_CHECK(row_off % 128 == 0, "p1_encode: staged chunks must start on a 128-row boundary");
+		if(X_dev) {
+			dim3 grid((unsigned) ((d + 31) / 32), (unsigned) ((rows + ENC_ROWS_PER_CTA - 1) / ENC_ROWS_PER_CTA)), block(32, 8);
+			p1_prof_begin(ctx, P1_K_ENCODE);
+			if(out->bits == 64) k_rows_to_cols_planes<uint64_t><<<grid, block, 0, ctx->stream>>>(X_dev, rows, d, row_off, (uint64_t *) out->xt, out->ld, out->stats, ep, out->planes, out->Lg);
+			else k_rows_to_cols_planes<uint32_t><<<grid, block, 0, ctx->stream>>>(X_dev, rows, d, row_off, (uint32_t *) out->xt, out->ld, out->stats, ep, out->planes, out->Lg);
+			P1_LAUNCHED(ctx);
+		}
+		if(y_dev) {
+			unsigned blocks = (unsigned) ((out->n + 256 * 16 - 1) / (256 * 16));
+			if(blocks > (unsigned) ctx->sm_count * 8) blocks = ctx->sm_count * 8;
+			const size_t pcol = (out->d + 1) * 128;
+			p1_prof_begin(ctx, P1_K_ENCODE);
+			if(out->bits == 64) k_vec_encode_planes<uint64_t><<<blocks, 256, 0, ctx->stream>>>(y_dev, out->n, (uint64_t *) out->xt + out->d * out->ld, out->stats + 4 * out->d, ep, out->planes + out->d * 128, pcol, out->Lg);
+			else k_vec_encode_planes<uint32_t><<<blocks, 256, 0, ctx->stream>>>(y_dev, out->n, (uint32_t *) out->xt + out->d * out->ld, out->stats + 4 * out->d, ep, out->planes + out->d * 128, pcol, out->Lg);
+			P1_LAUNCHED(ctx);
+		}
+		return 0;
+	}
 	if(X_dev) {
 		if(out->bits == 64) { if(launch_rows_to_cols<uint64_t, double>(ctx, X_dev, rows, d, row_off, out, ep)) return 1; }
 		else { if(launch_rows_to_cols<uint32_t, double>(ctx, X_dev, rows, d, row_off, out, ep)) return 1; }

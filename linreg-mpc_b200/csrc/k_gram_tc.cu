@@ -416,19 +416,30 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 
 	// digit planes P[kblock][l][a][128 rows], rows padded to a whole K-block
 	const size_t ldp = p1_round_up(data->ld, TC_BK);
-	const size_t need = (size_t) gs.m * ldp * L;
-	if(ctx->limb_ws_bytes < need) {
-		if(ctx->limb_ws) {
-			P1_CUDA(cudaStreamSynchronize(ctx->stream));
-			P1_CUDA(cudaFree(ctx->limb_ws));
-			ctx->limb_ws = NULL;
-			ctx->limb_ws_bytes = 0;
+	// The encode pass may have left the planes of every column already (p1_api.cu, option "encode_planes"):
+	// usable when they hold enough digits and the set is contiguous in the store's column order.
+	const bool pre = data->planes && L <= data->Lg && ldp == data->ld && (!owns_target || col_hi == data->d);
+	uint8_t *planes;
+	size_t col_stride, blk_stride;              // bytes between digits of a K-block, between K-blocks
+	if(pre) {
+		planes = data->planes + col_lo * TC_BK;
+		col_stride = (data->d + 1) * TC_BK;
+		blk_stride = col_stride * data->Lg;
+	} else {
+		const size_t need = (size_t) gs.m * ldp * L;
+		if(ctx->limb_ws_bytes < need) {
+			if(ctx->limb_ws) {
+				P1_CUDA(cudaStreamSynchronize(ctx->stream));
+				P1_CUDA(cudaFree(ctx->limb_ws));
+				ctx->limb_ws = NULL;
+				ctx->limb_ws_bytes = 0;
+			}
+			P1_CUDA(cudaMalloc(&ctx->limb_ws, need));
+			ctx->limb_ws_bytes = need;
 		}
-		P1_CUDA(cudaMalloc(&ctx->limb_ws, need));
-		ctx->limb_ws_bytes = need;
-	}
-	uint8_t *planes = (uint8_t *) ctx->limb_ws;
-	{
+		planes = (uint8_t *) ctx->limb_ws;
+		col_stride = (size_t) gs.m * TC_BK;
+		blk_stride = col_stride * L;
 		dim3 grid((unsigned) ((ldp + 1023) / 1024), (unsigned) gs.m);
 		p1_prof_begin(ctx, P1_K_GRAM_LIMBS);
 		if(data->bits == 64) k_limb_split<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *) data->xt, data->ld, gs, L, planes, ldp);
@@ -443,7 +454,7 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	if(!esz) { const char *e = getenv("P1_TMA_ELEM"); esz = e ? atoi(e) : 4; }
 	const CUtensorMapDataType dt = esz == 8 ? CU_TENSOR_MAP_DATA_TYPE_UINT64 : esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
 	cuuint64_t gdim[4] = {(cuuint64_t) (TC_BK / esz), (cuuint64_t) gs.m, (cuuint64_t) L, (cuuint64_t) (ldp / TC_BK)};
-	cuuint64_t gstr[3] = {TC_BK, (cuuint64_t) gs.m * TC_BK, (cuuint64_t) gs.m * TC_BK * L};
+	cuuint64_t gstr[3] = {TC_BK, (cuuint64_t) col_stride, (cuuint64_t) blk_stride};
 	cuuint32_t estr[4] = {1, 1, 1, 1};
 	cuuint32_t boxA[4] = {(cuuint32_t) (TC_BK / esz), TC_BM, (cuuint32_t) L, 1}, boxB[4] = {(cuuint32_t) (TC_BK / esz), TC_BN, (cuuint32_t) L, 1};
 	CUresult r1 = encode(&mapA, dt, 4, planes, gdim, gstr, boxA, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

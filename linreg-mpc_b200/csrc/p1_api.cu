@@ -73,6 +73,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->wire_ws_bytes = 0;
 	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
 	ctx->opt_ti_threads = 0;
+	ctx->opt_encode_planes = 0;
 	ctx->prof = false;
 	ctx->prof_open = -1;
 	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
@@ -142,6 +143,7 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "ti_threads must be a multiple of 32 in [32,512]");
 		ctx->opt_ti_threads = value;
 	}
+	else if(!strcmp(name, "encode_planes")) ctx->opt_encode_planes = value;
 	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
 	return 0;
 }
@@ -255,7 +257,7 @@ extern "C" int p1_copy_d2h(p1_ctx *ctx, void *dst, const void *src, size_t bytes
 // One retired column store per device is kept for the next p1_encode of the same size
 // (cudaMalloc/cudaFree of multi-GB buffers cost milliseconds and synchronise the device;
 // a provider re-encoding per run, and bench.py's step, hit this every time).
-struct StoreCache { void *xt; uint64_t *stats; size_t bytes, stat_bytes; };
+struct StoreCache { void *xt; uint64_t *stats; size_t bytes, stat_bytes; uint8_t *planes; size_t plane_bytes; };
 static StoreCache g_store[64] = {};
 static std::mutex g_store_mu;
 
@@ -270,7 +272,7 @@ __global__ void k_zero_pads(unsigned char *__restrict__ xt, size_t col_bytes, si
 	for(size_t i = 0; i < k; i++) p[i] = 0;
 }
 
-static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out) {
+static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out, int Lg = 0) {
 	p1_data *dt = new p1_data();
 	dt->device = ctx->device;
 	dt->bits = ctx->bits_p1;
@@ -280,7 +282,11 @@ static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out
 	dt->ld = p1_round_up(n ? n : 1, 256);
 	dt->xt = NULL;
 	dt->stats = NULL;
+	dt->planes = NULL;
+	dt->Lg = 0;
+	dt->plane_bytes = 0;
 	const size_t w = (size_t) (dt->bits / 8);
+	const size_t plane_bytes = (size_t) Lg * (d + 1) * dt->ld;
 	size_t bytes = (d + 1) * dt->ld * w, stat_bytes = (d + 1) * 4 * sizeof(uint64_t);
 	{
 		std::lock_guard<std::mutex> l(g_store_mu);
@@ -290,7 +296,23 @@ static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out
 			dt->stats = c.stats;
 			c.xt = NULL;
 			c.stats = NULL;
+			if(c.planes && c.plane_bytes == plane_bytes) {
+				dt->planes = c.planes;
+				c.planes = NULL;
+			}
 		}
+	}
+	if(plane_bytes && !dt->planes && cudaMalloc(&dt->planes, plane_bytes) != cudaSuccess) {
+		cudaGetLastError();
+		dt->planes = NULL;                 // no room for the planes: the Gram falls back to k_limb_split
+	}
+	if(dt->planes) {
+		dt->Lg = Lg;
+		dt->plane_bytes = plane_bytes;
+		// rows >= n of the last K-blocks must hold zero digits (an absent target column is never read:
+		// p1_local_block refuses owns_target without one)
+		const size_t kb0 = n / 128, per_kb = (size_t) Lg * (d + 1) * 128;
+		if(kb0 * 128 < dt->ld) cudaMemsetAsync(dt->planes + kb0 * per_kb, 0, (dt->ld / 128 - kb0) * per_kb, ctx->stream);
 	}
 	if(!dt->xt && (cudaMalloc(&dt->xt, bytes) != cudaSuccess || cudaMalloc(&dt->stats, stat_bytes) != cudaSuccess)) {
 		cudaError_t e = cudaGetLastError();
@@ -317,18 +339,23 @@ extern "C" void p1_data_free(p1_data *dt) {
 	cudaDeviceSynchronize();
 	void *old_xt = NULL;
 	uint64_t *old_stats = NULL;
+	uint8_t *old_planes = NULL;
 	{
 		std::lock_guard<std::mutex> l(g_store_mu);
 		StoreCache &c = g_store[dt->device & 63];
 		old_xt = c.xt;
 		old_stats = c.stats;
+		old_planes = c.planes;
 		c.xt = dt->xt;
 		c.stats = dt->stats;
 		c.bytes = dt->bytes;
 		c.stat_bytes = dt->stat_bytes;
+		c.planes = dt->planes;
+		c.plane_bytes = dt->plane_bytes;
 	}
 	if(old_xt) cudaFree(old_xt);
 	if(old_stats) cudaFree(old_stats);
+	if(old_planes) cudaFree(old_planes);
 	delete dt;
 }
 
@@ -338,8 +365,10 @@ static void store_cache_drop(int device) {
 	StoreCache &c = g_store[device & 63];
 	if(c.xt) cudaFree(c.xt);
 	if(c.stats) cudaFree(c.stats);
+	if(c.planes) cudaFree(c.planes);
 	c.xt = NULL;
 	c.stats = NULL;
+	c.planes = NULL;
 }
 
 extern "C" size_t p1_data_rows(const p1_data *dt) { return dt ? dt->n : 0; }
@@ -374,7 +403,16 @@ extern "C" int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n
 	P1_CHECK(n > 0 && d > 0, "p1_encode: empty matrix (%zu x %zu)", n, d);
 	P1_CHECK(precision >= 0 && precision < 63, "p1_encode: precision %d out of range", precision);
 	p1_data *dt = NULL;
-	if(data_alloc(ctx, n, d, y != NULL, &dt)) return 1;
+	// Digit planes for the tensor-core Gram, written in the same pass (saves k_limb_split's re-read of every
+	// word).  The digit count must be fixed before the data has been seen: enough for |value| <= 16 at this
+	// scale; if a block turns out to need more (statistics of this very pass), its Gram splits again itself.
+	int Lg = 0;
+	if(ctx->opt_encode_planes && n >= 4096) {
+		const double bound = 16.0 * (double) (1ll << precision) / normalizer;
+		if(bound < 9.0e15) Lg = p1_tc_digits((uint64_t) bound + 1, ctx->bits_p1 / 8);
+		if(Lg > 4) Lg = 0;
+	}
+	if(data_alloc(ctx, n, d, y != NULL, &dt, Lg)) return 1;
 	int st = 0;
 	if(p1_is_device_ptr(X)) {
 		st = p1_launch_encode(ctx, X, n, d, 0, NULL, normalizer, precision, dt);

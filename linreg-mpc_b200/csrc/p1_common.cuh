@@ -30,6 +30,7 @@ struct p1_ctx {
 	void *wire_ws;  size_t wire_ws_bytes;
 	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols;
 	long opt_ti_threads;              // threads per CTA of k_ti_generate (0 = default)
+	long opt_encode_planes;           // p1_encode also writes the digit planes of the tcgen05 Gram (0 = off)
 	// per-kernel-class event timing (p1_ctx_profile)
 	bool prof;
 	int prof_open;                       // class of the launch being bracketed, -1 if none
@@ -53,6 +54,9 @@ struct p1_data {
 	void *xt;           // (d+1) x ld ring words, column-major; rows >= n are zero
 	uint64_t *stats;    // (d+1) x 4 : sq_lo, sq_hi, viol, maxabs
 	size_t bytes, stat_bytes;   // allocation sizes of xt and stats
+	// digit planes written by the encode pass for the tcgen05 Gram (k_gram_tc.cu): P[row/128][l][column 0..d][128],
+	// Lg balanced base-256 digits per word; NULL when the encode pass did not produce them
+	uint8_t *planes; int Lg; size_t plane_bytes;
 };
 
 // error plumbing (check() of the reference: message to stderr, return 1)
@@ -83,6 +87,7 @@ bool p1_is_device_ptr(const void *p);
 int p1_small_to_dev(p1_ctx *ctx, const void *src, size_t bytes, size_t slot, const void **dev);
 
 // ---- launchers implemented in the kernel translation units ----
+int p1_tc_digits(uint64_t maxabs, int ring_bytes);
 int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
 	const double *y_dev, double normalizer, int precision, p1_data *out);
 int p1_launch_words_in(p1_ctx *ctx, const void *Xw_dev, const void *yw_dev, p1_data *out);

@@ -153,6 +153,9 @@ class Phase1Box:
             c = c_vp()
             lib.check(lib.p1_ctx_create(device, bits_p1, bits_p2, ctypes.byref(c)))
             self.ctxs.append(c)
+        # every provider's block is computed from this one column store, so the digit planes of all
+        # columns are used: let the encode pass write them (a single party would use only its own columns)
+        lib.check(lib.p1_ctx_set_option(self.ctxs[0], b"encode_planes", 1))
         self.data = None
         S, C = self.sched, self.sched.num_cross
         # one flat u64 buffer so that a single all-reduce combines row shards:

@@ -192,6 +192,55 @@ def test_local_block_tcgen05_shapes(p1lib, oracle, b1, b2, prec, prec2):
     p1lib.p1_ctx_destroy(ctx)
 
 
+def _limb_split_launches(p1lib, ctx):
+    from linreg_mpc_b200 import ffi
+    ms, cnt = ctypes.c_double(), ctypes.c_uint64()
+    p1lib.check(p1lib.p1_ctx_profile_read(ctx, ffi.P1_K_GRAM_LIMBS, ctypes.byref(ms), ctypes.byref(cnt)))
+    return cnt.value
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+@pytest.mark.parametrize("n,d", [(5000, 300), (70001, 37)])
+def test_encode_with_digit_planes(p1lib, oracle, b1, b2, prec, prec2, n, d):
+    """option encode_planes: the encode pass also writes the digit planes of the tcgen05 Gram.
+    Words, statistics and every Gram block must equal the two-pass result, and the Gram must
+    not run its own digit split (except where the planes cannot serve it)."""
+    X, y, _ = po.generate_lin_regression(n, d, seed=5)
+    nz = oracle.normalizer(prec, n)
+    ctx = mkctx(p1lib, b1, b2)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_planes", 1))
+    p1lib.check(p1lib.p1_ctx_profile(ctx, 1))
+    data = encode(p1lib, ctx, X, y, nz, prec)
+    Xw, yw = download(p1lib, ctx, data, n, d, b1)
+    assert np.array_equal(Xw, oracle.encode(X, nz, prec, b1, b2))
+    assert np.array_equal(yw, oracle.encode(y, nz, prec, b1, b2))
+    digits = ctypes.c_int()
+    p1lib.check(p1lib.p1_gram_digits(ctx, data, 0, d, 1, ctypes.byref(digits)))
+    planes_serve = digits.value <= 4                      # more digits than the encode pass provided: split again
+    base = _limb_split_launches(p1lib, ctx)
+    lo, hi = d // 3, d - d // 4
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, b1, 2)        # single provider
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, lo, hi, False, b1, 2)     # middle provider
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, hi, d, True, b1, 2)       # last provider
+    if planes_serve:
+        assert _limb_split_launches(p1lib, ctx) == base
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, hi, True, b1, 2)       # target with a non-adjacent block: own split
+    assert _limb_split_launches(p1lib, ctx) > base
+    p1lib.p1_data_free(data)
+    # values far beyond the planes' digit budget: the Gram falls back to its own split
+    data = encode(p1lib, ctx, X * 4096.0, y, nz, prec)
+    Xw, yw = download(p1lib, ctx, data, n, d, b1)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, b1, 2)
+    p1lib.p1_data_free(data)
+    # no target vector
+    out = c_vp()
+    p1lib.check(p1lib.p1_encode(ctx, vp(X), None, n, d, nz, prec, ctypes.byref(out)))
+    Xw, _ = download(p1lib, ctx, out, n, d, b1, with_y=False)
+    _check_local_block(p1lib, oracle, ctx, out, Xw, None, 0, d, False, b1, 2)
+    p1lib.p1_data_free(out)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 @pytest.mark.parametrize("bits", [64, 32])
 def test_diagonal_exact_and_sequential(p1lib, oracle, bits):
     b2 = bits
