@@ -180,26 +180,23 @@ __device__ __forceinline__ void enc_store4(W *dst, const W (&w)[4]) {
 	}
 }
 
-// digits of 4 words, digit l of all four packed into one 32-bit store at dst + l*stride
+// Digits of 4 words, digit l of all four packed into one 32-bit store at dst + l*stride (Lg <= 4).
+// The balanced base-256 digits d_l in [-128,127] of v mod 2^32 are the bytes of (v + 0x80808080) with bit 7
+// flipped back: v + sum 128*256^l = sum b_l 256^l  =>  d_l = b_l - 128 = (s8)(b_l ^ 0x80).  Only the low 32 bits
+// of a word matter for the first four digits; a word that does not fit Lg digits makes the Gram split again
+// (its digit count comes from the max |word| statistic), so the planes are never used for it.
 template <typename W>
 __device__ __forceinline__ void enc_digits4(const W (&w)[4], uint8_t *dst, size_t stride, int Lg) {
-	typedef typename p1_word<W>::s S;
-	int64_t v[4];
+	uint32_t t[4];
 #pragma unroll
-	for(int i = 0; i < 4; i++) v[i] = (int64_t) (S) w[i];
-#pragma unroll
-	for(int l = 0; l < 4; l++) {
-		if(l < Lg) {
-			uint32_t packed = 0;
-#pragma unroll
-			for(int i = 0; i < 4; i++) {
-				const int64_t dg = (int64_t) (int8_t) (v[i] & 0xff);
-				v[i] = (v[i] - dg) >> 8;
-				packed |= ((uint32_t) dg & 0xffu) << (8 * i);
-			}
-			*reinterpret_cast<uint32_t *>(dst + (size_t) l * stride) = packed;
-		}
-	}
+	for(int i = 0; i < 4; i++) t[i] = ((uint32_t) w[i] + 0x80808080u) ^ 0x80808080u;
+	// 4x4 byte transpose: word i byte l -> digit l byte i
+	const uint32_t a = __byte_perm(t[0], t[1], 0x5140), b = __byte_perm(t[2], t[3], 0x5140);
+	const uint32_t c = __byte_perm(t[0], t[1], 0x7362), d = __byte_perm(t[2], t[3], 0x7362);
+	*reinterpret_cast<uint32_t *>(dst) = __byte_perm(a, b, 0x5410);
+	if(Lg > 1) *reinterpret_cast<uint32_t *>(dst + stride) = __byte_perm(a, b, 0x7632);
+	if(Lg > 2) *reinterpret_cast<uint32_t *>(dst + 2 * stride) = __byte_perm(c, d, 0x5410);
+	if(Lg > 3) *reinterpret_cast<uint32_t *>(dst + 3 * stride) = __byte_perm(c, d, 0x7632);
 }
 
 template <typename W, bool FULL>

@@ -78,6 +78,7 @@ def main():
         C = loop(box, key, mode)
         dt = time.perf_counter() - t0
         out[mode + "_ms_per_batch"] = round(dt * 1e3 / (C / batch), 4)
+        out[mode + "_us_per_pair"] = round(dt * 1e6 / C, 3)
     print(json.dumps(out))
     box.close()
 
