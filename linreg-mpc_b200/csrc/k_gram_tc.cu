@@ -450,9 +450,8 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	// tensor maps over the planes: dims (row in block, column, limb, block), u8, 128-byte swizzle
 	CUtensorMap mapA, mapB;
 	// (declared as 32-bit elements: the swizzle and the bytes moved are the same as for u8)
-	static int esz = 0;
-	if(!esz) { const char *e = getenv("P1_TMA_ELEM"); esz = e ? atoi(e) : 4; }
-	const CUtensorMapDataType dt = esz == 8 ? CU_TENSOR_MAP_DATA_TYPE_UINT64 : esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+	const int esz = 4;
+	const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_UINT32;
 	cuuint64_t gdim[4] = {(cuuint64_t) (TC_BK / esz), (cuuint64_t) gs.m, (cuuint64_t) L, (cuuint64_t) (ldp / TC_BK)};
 	cuuint64_t gstr[3] = {TC_BK, (cuuint64_t) col_stride, (cuuint64_t) blk_stride};
 	cuuint32_t estr[4] = {1, 1, 1, 1};

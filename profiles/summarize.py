@@ -44,7 +44,9 @@ def full(rep, out):
             for m in METRICS:
                 if m in idx and r[idx[m]] != "":
                     f.write("%-75s %s %s\n" % (m, r[idx[m]], units[idx[m]]))
-            tens = [h for h in hdr if "tensor" in h and h not in METRICS and r[idx[h]] not in ("", "0")]
+            # any other tensor-pipe activity counter (not the constant peak_sustained / attribute columns)
+            tens = [h for h in hdr if "tensor" in h and h not in METRICS and "peak_sustained" not in h.split(".")[-1]
+                    and not h.startswith("device__") and "ops_path" not in h and r[idx[h]] not in ("", "0")]
             for m in tens[:12]:
                 f.write("%-75s %s %s\n" % (m, r[idx[m]], units[idx[m]]))
 
