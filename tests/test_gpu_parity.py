@@ -241,6 +241,41 @@ def test_encode_with_digit_planes(p1lib, oracle, b1, b2, prec, prec2, n, d):
     p1lib.p1_ctx_destroy(ctx)
 
 
+@pytest.mark.parametrize("b1,b2,prec", [(64, 64, 56), (32, 32, 24)])
+def test_encode_with_digit_planes_staged_host_input(p1lib, oracle, b1, b2, prec):
+    """host rows larger than one staging chunk (256 MB): the chunks of the encode pass land at row offsets
+    > 0 of the column store and of the digit planes; the Gram from the planes must equal the Gram that
+    splits the stored words itself (verified against the oracle in the tests above), word for word."""
+    n, d = 300_001, 128                      # 307 MB of doubles: chunks of 262144 + 37857 rows
+    rng = np.random.default_rng(8)
+    X = rng.standard_normal((n, d))
+    y = rng.standard_normal(n)
+    nz = oracle.normalizer(prec, n)
+    L = int(p1lib.p1_acc_len(d))
+    accs = []
+    for planes in (1, 0):
+        ctx = mkctx(p1lib, b1, b2)
+        p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_planes", planes))
+        p1lib.check(p1lib.p1_ctx_profile(ctx, 1))
+        data = encode(p1lib, ctx, X, y, nz, prec)
+        if planes:
+            Xw, yw = download(p1lib, ctx, data, n, d, b1)
+            assert np.array_equal(Xw[::997], oracle.encode(X[::997], nz, prec, b1, b2))
+            assert np.array_equal(Xw[-300:], oracle.encode(X[-300:], nz, prec, b1, b2))
+            assert np.array_equal(yw, oracle.encode(y, nz, prec, b1, b2))
+        acc = dev_zeros(p1lib, ctx, 8 * L)
+        p1lib.check(p1lib.p1_local_block(ctx, data, 0, d, 1, acc, 2))
+        accs.append(to_host(p1lib, ctx, acc, L, np.uint64))
+        assert (_limb_split_launches(p1lib, ctx) == 0) == bool(planes)
+        if planes:
+            i, j = 77, 5
+            assert int(accs[0][i * (i + 1) // 2 + j]) & ((1 << b1) - 1) == oracle.dot(Xw[:, i], Xw[:, j], b1)
+        p1lib.check(p1lib.p1_dev_free(ctx, acc))
+        p1lib.p1_data_free(data)
+        p1lib.p1_ctx_destroy(ctx)
+    assert np.array_equal(accs[0], accs[1])
+
+
 @pytest.mark.parametrize("bits", [64, 32])
 def test_diagonal_exact_and_sequential(p1lib, oracle, bits):
     b2 = bits
