@@ -84,7 +84,12 @@ const char *p1_kernel_class_name(int kernel_class);
  *   "gram_tc_max_slices"   : upper bound on the row slices (grid.y) of k_gram_tc
  *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
  *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on
- *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM) */
+ *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM)
+ *   "encode_planes"        : 1 = p1_encode also writes, in the same pass, the base-256 digit planes of ALL
+ *                            columns that the tcgen05 Gram reads (no digit split before p1_local_block; +3..4
+ *                            bytes of HBM per word).  Worth it when one p1_data serves every provider's block
+ *                            (a box that holds all columns); a single party multiplies only its own columns
+ *                            and leaves it off (default 0).  Results are identical either way. */
 int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
 
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);

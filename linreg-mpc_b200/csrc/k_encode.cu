@@ -3,6 +3,8 @@
 //                    fixed-point encode fused (src/linear.c:46-51, src/fixed.c:3-5) and
 //                    per-column statistics gathered in the same pass.
 //   k_vec_encode   : same for the target vector (src/linear.c:83-87).
+//   k_rows_to_cols_planes / k_vec_encode_planes : the same passes, also writing the digit planes
+//                    of the tcgen05 Gram (option encode_planes).
 //   k_cols_to_rows : column-major -> the reference's row-major layout (tests / download).
 #include "p1_common.cuh"
 #include <type_traits>
