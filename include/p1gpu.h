@@ -85,6 +85,8 @@ const char *p1_kernel_class_name(int kernel_class);
  *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
  *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on
  *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM)
+ *   "encode_async"         : 0 = never use the cp.async pipeline kernel of p1_encode (default 1: used whenever d
+ *                            is even and the source is 16-byte aligned; identical results)
  *   "encode_planes"        : 1 = p1_encode also writes, in the same pass, the base-256 digit planes of ALL
  *                            columns that the tcgen05 Gram reads (no digit split before p1_local_block; +3..4
  *                            bytes of HBM per word).  Worth it when one p1_data serves every provider's block

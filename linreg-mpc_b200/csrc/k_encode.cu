@@ -305,6 +305,118 @@ __global__ void __launch_bounds__(256) k_vec_encode_planes(const double *__restr
 	if((threadIdx.x & 31) == 0) cs.flush(stats);
 }
 
+// ------------------------------------------------------------------ encode through an async-copy pipeline
+//
+// k_encode_async: the source tile goes global -> shared with 16-byte cp.async (no registers held by loads in
+// flight), ENC_A_STAGES tiles of 64 rows x 32 columns per CTA in a ring, one __syncthreads per tile.  The
+// 16-byte chunks of a tile row are XOR-swizzled with (row/4)%16, so that the transposed read - a half-warp
+// per column, a lane per group of 4 consecutive rows, odd/even columns in the two halves - touches every bank
+// pair exactly twice per 64-bit warp load (the minimum).  Each thread then owns 4 consecutive rows of a column:
+// one 32/16-byte word store and, with PLANES, one packed 32-bit store per digit (see enc_digits4).
+// Needs an even d and a 16-byte aligned source (every chunk is then 16-byte aligned and never straddles the
+// last column); the other cases take the kernels above.
+#define ENC_A_ROWS 64
+#define ENC_A_STAGES 4
+#define ENC_A_ROWS_PER_CTA 1024
+#define ENC_A_STAGE_BYTES (ENC_A_ROWS * 32 * 8)
+
+__device__ __forceinline__ void enc_cp_async16(uint32_t dst_smem, const void *src, bool valid) {
+	const int sz = valid ? 16 : 0;                       // src-size 0: the 16 bytes are zero-filled
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(sz) : "memory");
+}
+
+template <typename W, bool PLANES>
+__global__ void __launch_bounds__(256, 3) k_encode_async(const double *__restrict__ src, size_t rows, size_t d, size_t row_off,
+	W *__restrict__ xt, size_t ld, uint64_t *__restrict__ stats, EncodeParams ep, uint8_t *__restrict__ planes, int Lg) {
+	extern __shared__ __align__(128) unsigned char enc_smem[];
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	const size_t c0 = (size_t) blockIdx.x * 32;
+	const size_t rbase = (size_t) blockIdx.y * ENC_A_ROWS_PER_CTA;
+	const size_t rend = rbase + ENC_A_ROWS_PER_CTA < rows ? rbase + ENC_A_ROWS_PER_CTA : rows;
+	const int ntiles = (int) ((rend - rbase + ENC_A_ROWS - 1) / ENC_A_ROWS);
+	const uint32_t smem0 = (uint32_t) __cvta_generic_to_shared(enc_smem);
+
+	// producer side: chunk id = tid + 256k -> row id/16, chunk id%16
+	auto issue = [&](int t) {
+		if(t < ntiles) {
+			const size_t r0 = rbase + (size_t) t * ENC_A_ROWS;
+			const uint32_t stage = smem0 + (uint32_t) (t % ENC_A_STAGES) * ENC_A_STAGE_BYTES;
+#pragma unroll
+			for(int k = 0; k < 4; k++) {
+				const int id = tid + 256 * k, row = id >> 4, ch = id & 15;
+				const size_t r = r0 + row, c = c0 + 2 * ch;
+				const bool valid = r < rend && c < d;
+				const double *g = valid ? src + r * d + c : src;
+				enc_cp_async16(stage + row * 256 + ((ch ^ ((row >> 2) & 15)) << 4), g, valid);
+			}
+		}
+		asm volatile("cp.async.commit_group;" ::: "memory");
+	};
+#pragma unroll
+	for(int t = 0; t < ENC_A_STAGES - 1; t++) issue(t);
+
+	// consumer side: half h of the warp takes the odd/even column of a pair, lane g the rows 4g..4g+3
+	const int h = lane >> 4, g = lane & 15;
+	ColStats cs[2];
+	cs[0].init();
+	cs[1].init();
+	const size_t pcol = (d + 1) * 128;
+#pragma unroll 1
+	for(int t = 0; t < ntiles; t++) {
+		asm volatile("cp.async.wait_group %0;" ::"n"(ENC_A_STAGES - 2) : "memory");
+		__syncthreads();
+		issue(t + ENC_A_STAGES - 1);                     // refills the stage consumed in iteration t-1
+		const size_t r0 = rbase + (size_t) t * ENC_A_ROWS;
+		const unsigned char *stage = enc_smem + (size_t) (t % ENC_A_STAGES) * ENC_A_STAGE_BYTES;
+		const size_t r4 = r0 + 4 * g;
+		if(r4 < rend) {
+#pragma unroll
+			for(int u = 0; u < 2; u++) {
+				const int cc = 2 * (warp + 8 * u) + h;
+				const size_t c = c0 + cc;
+				if(c < d) {
+					W w[4];
+#pragma unroll
+					for(int i = 0; i < 4; i++) {
+						const double v = *reinterpret_cast<const double *>(stage + (4 * g + i) * 256 + ((((cc >> 1) ^ g) << 4) | ((cc & 1) << 3)));
+						w[i] = load_word<W, double>(v, ep);          // rows >= rend were zero-filled: word 0
+					}
+					W *dst = xt + c * ld + row_off + r4;
+					if(r4 + 4 <= rend) {
+						enc_store4<W>(dst, w);
+#pragma unroll
+						for(int i = 0; i < 4; i++) cs[u].add<W>(w[i]);
+					} else {
+#pragma unroll
+						for(int i = 0; i < 4; i++) if(r4 + i < rend) { dst[i] = w[i]; cs[u].add<W>(w[i]); }
+					}
+					if(PLANES) {
+						const size_t rg = row_off + r4;
+						enc_digits4<W>(w, planes + (rg >> 7) * (size_t) Lg * pcol + c * 128 + (rg & 127), pcol, Lg);
+					}
+				}
+			}
+		}
+	}
+	asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+	for(int u = 0; u < 2; u++) {
+		// reduce over the 16 lanes of the half (xor 8,4,2,1 stays inside it)
+		cs[u].sq = cs[u].sq + __shfl_xor_sync(0xffffffffu, cs[u].sq, 8);
+		cs[u].sq = cs[u].sq + __shfl_xor_sync(0xffffffffu, cs[u].sq, 4);
+		cs[u].sq = cs[u].sq + __shfl_xor_sync(0xffffffffu, cs[u].sq, 2);
+		cs[u].sq = cs[u].sq + __shfl_xor_sync(0xffffffffu, cs[u].sq, 1);
+#pragma unroll
+		for(int o = 8; o; o >>= 1) {
+			cs[u].viol += __shfl_xor_sync(0xffffffffu, cs[u].viol, o);
+			const uint64_t m = __shfl_xor_sync(0xffffffffu, cs[u].mx, o);
+			cs[u].mx = m > cs[u].mx ? m : cs[u].mx;
+		}
+		const size_t c = c0 + 2 * (warp + 8 * u) + h;
+		if(g == 0 && c < d) cs[u].flush(stats + 4 * c);
+	}
+}
+
 template <typename W, typename SRC>
 __global__ void __launch_bounds__(256) k_vec_encode(const SRC *__restrict__ src, size_t n, W *__restrict__ col,
 	uint64_t *__restrict__ stats, EncodeParams ep) {
@@ -362,6 +474,21 @@ static int launch_vec(p1_ctx *ctx, const SRC *src, p1_data *out, EncodeParams ep
 int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
 	const double *y_dev, double normalizer, int precision, p1_data *out) {
 	EncodeParams ep = {normalizer, (double) (1ll << precision), ctx->bits_p2};
+	// async-copy pipeline: needs 16-byte aligned chunks (even d, aligned source) and 128-row aligned chunk starts
+	if(X_dev && ctx->opt_encode_async && d % 2 == 0 && ((uintptr_t) X_dev & 15) == 0 && row_off % 128 == 0) {
+		dim3 grid((unsigned) ((d + 31) / 32), (unsigned) ((rows + ENC_A_ROWS_PER_CTA - 1) / ENC_A_ROWS_PER_CTA));
+		const int smem = ENC_A_STAGES * ENC_A_STAGE_BYTES;
+		p1_prof_begin(ctx, P1_K_ENCODE);
+#define ENC_A_LAUNCH(W, PL) do { \
+			P1_CUDA(cudaFuncSetAttribute(k_encode_async<W, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+			k_encode_async<W, PL><<<grid, 256, smem, ctx->stream>>>(X_dev, rows, d, row_off, (W *) out->xt, out->ld, out->stats, ep, out->planes, out->Lg); \
+		} while(0)
+		if(out->bits == 64) { if(out->planes) ENC_A_LAUNCH(uint64_t, true); else ENC_A_LAUNCH(uint64_t, false); }
+		else { if(out->planes) ENC_A_LAUNCH(uint32_t, true); else ENC_A_LAUNCH(uint32_t, false); }
+#undef ENC_A_LAUNCH
+		P1_LAUNCHED(ctx);
+		X_dev = NULL;                                    // the matrix is done; the target vector follows below
+	}
 	if(out->planes) {
 		// one pass that also writes the digit planes of the tensor-core Gram
 		P1_CHECK(row_off % 128 == 0, "p1_encode: staged chunks must start on a 128-row boundary");

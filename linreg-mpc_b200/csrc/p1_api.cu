@@ -74,6 +74,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
 	ctx->opt_ti_threads = 0;
 	ctx->opt_encode_planes = 0;
+	ctx->opt_encode_async = 1;
 	ctx->prof = false;
 	ctx->prof_open = -1;
 	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
@@ -144,6 +145,7 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 		ctx->opt_ti_threads = value;
 	}
 	else if(!strcmp(name, "encode_planes")) ctx->opt_encode_planes = value;
+	else if(!strcmp(name, "encode_async")) ctx->opt_encode_async = value;
 	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
 	return 0;
 }

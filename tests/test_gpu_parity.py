@@ -200,8 +200,54 @@ def _limb_split_launches(p1lib, ctx):
 
 
 @pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
+@pytest.mark.parametrize("n,d", [(4503, 64), (1030, 500)])
+def test_encode_async_pipeline_and_fallbacks(p1lib, oracle, b1, b2, prec, prec2, n, d):
+    """the cp.async encode kernel (even d, 16-byte aligned source; the default) against the oracle, with the x86
+    cast edge cases, ragged row tiles and a ragged last column tile; the same input at an 8-byte aligned
+    address and with the pipeline switched off must take the register-staged kernels and give the same words
+    and the same statistics (through the exact diagonal)"""
+    import torch
+    rng = np.random.default_rng(12)
+    X = rng.standard_normal((n, d))
+    y = rng.standard_normal(n)
+    X[0, :8] = [1e30, -1e30, float("nan"), float("inf"), float("-inf"), 0.0, -0.0, 5e-324]
+    X[n - 1, d - 4:] = [2.0 ** 31, -2.0 ** 31, 2.0 ** 63, -2.0 ** 63]
+    nz = oracle.normalizer(prec, n)
+    want = oracle.encode(X, nz, prec, b1, b2)
+    flat = torch.zeros(n * d + 1, dtype=torch.float64, device="cuda")
+    flat[1:] = torch.from_numpy(X).cuda().reshape(-1)
+    Xal = torch.from_numpy(X).cuda()
+    assert Xal.data_ptr() % 16 == 0 and flat[1:].data_ptr() % 16 == 8
+    L = int(p1lib.p1_acc_len(d))
+    accs = []
+    for name, ptr_, async_ in (("pipeline", Xal.data_ptr(), 1), ("unaligned", flat[1:].data_ptr(), 1), ("off", Xal.data_ptr(), 0), ("host", None, 1)):
+        ctx = mkctx(p1lib, b1, b2)
+        p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_async", async_))
+        out = c_vp()
+        p1lib.check(p1lib.p1_encode(ctx, c_vp(ptr_) if ptr_ else vp(X), vp(y), n, d, nz, prec, ctypes.byref(out)))
+        Xw, yw = download(p1lib, ctx, out, n, d, b1)
+        assert np.array_equal(Xw, want), name
+        assert np.array_equal(yw, oracle.encode(y, nz, prec, b1, b2)), name
+        acc = dev_zeros(p1lib, ctx, 8 * L)
+        p1lib.check(p1lib.p1_local_block(ctx, out, 0, d, 1, acc, 1))
+        accs.append(to_host(p1lib, ctx, acc, L, np.uint64))
+        p1lib.check(p1lib.p1_dev_free(ctx, acc))
+        p1lib.p1_data_free(out)
+        p1lib.p1_ctx_destroy(ctx)
+    nA = d * (d + 1) // 2
+    with np.errstate(over="ignore"):
+        for a in accs[1:]:
+            assert np.array_equal(a[:nA + d], accs[0][:nA + d])                        # ring words
+            assert np.array_equal(a[nA + 3 * d:], accs[0][nA + 3 * d:])                # |word| >= 2^26 counts
+            # sum of squares = (hi << 32) + lo; how it splits into the two rows depends on the flush grouping
+            sq = lambda v: (v[nA + 2 * d:nA + 3 * d] << np.uint64(32)) + v[nA + d:nA + 2 * d]
+            assert np.array_equal(sq(a), sq(accs[0]))
+
+
+@pytest.mark.parametrize("async_", [1, 0])
+@pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
 @pytest.mark.parametrize("n,d", [(5000, 300), (70001, 37)])
-def test_encode_with_digit_planes(p1lib, oracle, b1, b2, prec, prec2, n, d):
+def test_encode_with_digit_planes(p1lib, oracle, b1, b2, prec, prec2, n, d, async_):
     """option encode_planes: the encode pass also writes the digit planes of the tcgen05 Gram.
     Words, statistics and every Gram block must equal the two-pass result, and the Gram must
     not run its own digit split (except where the planes cannot serve it)."""
@@ -209,6 +255,7 @@ def test_encode_with_digit_planes(p1lib, oracle, b1, b2, prec, prec2, n, d):
     nz = oracle.normalizer(prec, n)
     ctx = mkctx(p1lib, b1, b2)
     p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_planes", 1))
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_async", async_))
     p1lib.check(p1lib.p1_ctx_profile(ctx, 1))
     data = encode(p1lib, ctx, X, y, nz, prec)
     Xw, yw = download(p1lib, ctx, data, n, d, b1)
