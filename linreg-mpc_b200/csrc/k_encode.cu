@@ -431,12 +431,12 @@ __global__ void __launch_bounds__(256) k_vec_encode(const SRC *__restrict__ src,
 	if((threadIdx.x & 31) == 0) cs.flush(stats);
 }
 
-// grid (ceil(d/32), ceil(n/32)), block (32,8): column-major -> row-major
+// grid (ceil(n/32), ceil(d/32)), block (32,8): column-major -> row-major (rows on grid.x: no 65535 limit)
 template <typename W>
 __global__ void __launch_bounds__(256) k_cols_to_rows(const W *__restrict__ xt, size_t ld, size_t n, size_t d, W *__restrict__ dst) {
 	__shared__ W tile[32][33];
 	const int tx = threadIdx.x, ty = threadIdx.y;
-	const size_t c0 = (size_t) blockIdx.x * 32, r0 = (size_t) blockIdx.y * 32;
+	const size_t c0 = (size_t) blockIdx.y * 32, r0 = (size_t) blockIdx.x * 32;
 #pragma unroll
 	for(int u = 0; u < 4; u++) {
 		int cc = ty + 8 * u;
@@ -474,6 +474,15 @@ static int launch_vec(p1_ctx *ctx, const SRC *src, p1_data *out, EncodeParams ep
 int p1_launch_encode(p1_ctx *ctx, const double *X_dev, size_t rows, size_t d, size_t row_off,
 	const double *y_dev, double normalizer, int precision, p1_data *out) {
 	EncodeParams ep = {normalizer, (double) (1ll << precision), ctx->bits_p2};
+	// grid.y carries the row tiles (<= 65535): longer matrices go in slabs of 2^24 rows
+	const size_t slab = (size_t) 1 << 24;
+	if(X_dev && rows > slab) {
+		for(size_t r = 0; r < rows; r += slab) {
+			const size_t part = rows - r < slab ? rows - r : slab;
+			if(p1_launch_encode(ctx, X_dev + r * d, part, d, row_off + r, NULL, normalizer, precision, out)) return 1;
+		}
+		X_dev = NULL;
+	}
 	// async-copy pipeline: needs 16-byte aligned chunks (even d, aligned source) and 128-row aligned chunk starts
 	if(X_dev && ctx->opt_encode_async && d % 2 == 0 && ((uintptr_t) X_dev & 15) == 0 && row_off % 128 == 0) {
 		dim3 grid((unsigned) ((d + 31) / 32), (unsigned) ((rows + ENC_A_ROWS_PER_CTA - 1) / ENC_A_ROWS_PER_CTA));
@@ -536,7 +545,7 @@ int p1_launch_words_in(p1_ctx *ctx, const void *Xw, const void *yw, p1_data *out
 int p1_launch_words_out(p1_ctx *ctx, const p1_data *dt, void *Xw, void *yw) {
 	size_t w = (size_t) dt->bits / 8;
 	if(Xw) {
-		dim3 grid((unsigned) ((dt->d + 31) / 32), (unsigned) ((dt->n + 31) / 32)), block(32, 8);
+		dim3 grid((unsigned) ((dt->n + 31) / 32), (unsigned) ((dt->d + 31) / 32)), block(32, 8);
 		p1_prof_begin(ctx, P1_K_LAYOUT);
 		if(dt->bits == 64) k_cols_to_rows<uint64_t><<<grid, block, 0, ctx->stream>>>((const uint64_t *) dt->xt, dt->ld, dt->n, dt->d, (uint64_t *) Xw);
 		else k_cols_to_rows<uint32_t><<<grid, block, 0, ctx->stream>>>((const uint32_t *) dt->xt, dt->ld, dt->n, dt->d, (uint32_t *) Xw);

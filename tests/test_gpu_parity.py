@@ -244,6 +244,26 @@ def test_encode_async_pipeline_and_fallbacks(p1lib, oracle, b1, b2, prec, prec2,
             assert np.array_equal(sq(a), sq(accs[0]))
 
 
+@pytest.mark.parametrize("d,async_", [(2, 1), (2, 0), (3, 1)])
+def test_encode_more_rows_than_one_grid(p1lib, oracle, d, async_):
+    """a device-resident matrix of more than 2^24 rows is encoded in row slabs (grid.y holds <= 65535 tiles)"""
+    import torch
+    n = (1 << 24) + 1000
+    g = torch.Generator(device="cuda"); g.manual_seed(31)
+    Xd = torch.randn((n, d), dtype=torch.float64, device="cuda", generator=g)
+    yd = torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
+    nz = oracle.normalizer(56, n)
+    ctx = mkctx(p1lib, 64, 64)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"encode_async", async_))
+    out = c_vp()
+    p1lib.check(p1lib.p1_encode(ctx, c_vp(Xd.data_ptr()), c_vp(yd.data_ptr()), n, d, nz, 56, ctypes.byref(out)))
+    Xw, yw = download(p1lib, ctx, out, n, d, 64)
+    assert np.array_equal(Xw, oracle.encode(Xd.cpu().numpy(), nz, 56, 64, 64))
+    assert np.array_equal(yw, oracle.encode(yd.cpu().numpy(), nz, 56, 64, 64))
+    p1lib.p1_data_free(out)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 @pytest.mark.parametrize("async_", [1, 0])
 @pytest.mark.parametrize("b1,b2,prec,prec2", WIDTHS)
 @pytest.mark.parametrize("n,d", [(5000, 300), (70001, 37)])
