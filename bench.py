@@ -37,6 +37,9 @@ WORKLOADS = {
     "cfg2": dict(n=100_000, d=100, p=3, bits_p1=64, bits_p2=64, precision=56, precision_p2=0),
     "cfg4": dict(n=10_000_000, d=200, p=1, bits_p1=32, bits_p2=32, precision=30, precision_p2=0),
     "cfg5": dict(n=1_000_000, d=1000, p=1, bits_p1=64, bits_p2=32, precision=56, precision_p2=30),
+    # the multi-provider variants of configs 4 and 5: 16 160 and 475 950 cross pairs
+    "cfg4p5": dict(n=10_000_000, d=200, p=5, bits_p1=32, bits_p2=32, precision=30, precision_p2=0),
+    "cfg5p20": dict(n=1_000_000, d=1000, p=20, bits_p1=64, bits_p2=32, precision=56, precision_p2=30),
     "gram": dict(n=1_000_000, d=500, p=1, bits_p1=64, bits_p2=64, precision=56, precision_p2=0),
     "tiny": dict(n=65_536, d=40, p=5, bits_p1=64, bits_p2=64, precision=56, precision_p2=0),
 }
