@@ -73,6 +73,7 @@ enum {
 	P1_K_MSG_UNPACK,      /* k_unpack_count / k_unpack_scan / k_unpack_write */
 	P1_K_SHARE_BITS,      /* k_share_bits */
 	P1_K_TEXT,            /* k_tok_count / k_tok_scan* / k_tok_parse */
+	P1_K_MASKING_FUSED,   /* k_masking_fused */
 	P1_K_COUNT
 };
 int p1_ctx_profile(p1_ctx *ctx, int enable);
@@ -85,6 +86,7 @@ const char *p1_kernel_class_name(int kernel_class);
  *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
  *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on
  *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM)
+ *   "fused_threads"        : same for the fused masking-loop kernel (p1_masking_fused)
  *   "encode_async"         : 0 = never use the cp.async pipeline kernel of p1_encode (default 1: used whenever d
  *                            is even and the source is 16-byte aligned; identical results)
  *   "encode_planes"        : 1 = p1_encode also writes, in the same pass, the base-256 digit planes of ALL
@@ -209,6 +211,31 @@ int p1_party_a_step(p1_ctx *ctx, const p1_data *data, const int32_t *cols, const
 int p1_party_b_share(p1_ctx *ctx, const p1_data *data, const int32_t *cols, const int64_t *slots, size_t count,
                      const void *in_dev, size_t ld_in, uint64_t *acc_dev);
 int p1_acc_sub_values(p1_ctx *ctx, uint64_t *acc_dev, const int64_t *slots, const uint64_t *value_dev, size_t count);
+
+/* ------------------------------------------------------------------ a9 + a10 fused: one box, all parties
+ * The body of the TI loop (src/phase1.c:270-278) and both parties' inner_product_ti
+ * (:187-195 and :202-205,221) for cross pairs q0 .. q0+count-1 whose two owners both live in
+ * `data` (all columns of the instance on this GPU: a single-box deployment, or one row shard
+ * of it).  One persistent kernel: the masks x, y of a pair are expanded (same stream as
+ * p1_ti_generate) and consumed in registers, so they never touch HBM; the two party messages
+ * are the protocol's data plane and ARE written:
+ *     msg_b[p][k] = col_b[k] + x[k]        (b -> a, :203-205)
+ *     msg_a[p][k] = col_a[k] - y[k]        (a -> b, :188-190)
+ *     xy[p]             = sum_k x[k] * y[k]               (WRITTEN; the TI's value_a = xy - r)
+ *     acc[slots_a[p]]  += sum_k msg_b[p][k] * y[k]        (:195)
+ *     acc[slots_b[p]]  += sum_k msg_a[p][k] * col_b[k]    (:221)
+ *     r[p]              = S[W0 + 2 n_total]               (:273; NULL to skip)
+ * cols_a[p] / cols_b[p] = row i / row j of the pair (column index into `data`, d = target);
+ * slots_*: absolute accumulator indices (the providers' accumulators may be slices of one
+ * buffer).  The four index arrays: host or device.  x_dev / y_dev (count vectors, ld_words
+ * apart) may be given to ALSO materialise the masks (tests: identical words to the split
+ * kernels), normally NULL.  `- value` is applied afterwards as for the split path
+ * (p1_ti_values, p1_acc_sub_values).  Rows: data's shard [row0, row0 + rows(data)) of n_total. */
+int p1_masking_fused(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total, size_t row0,
+                     const p1_data *data, const int32_t *cols_a, const int32_t *cols_b,
+                     const int64_t *slots_a, const int64_t *slots_b,
+                     void *msg_b_dev, void *msg_a_dev, size_t ld_words, void *x_dev, void *y_dev,
+                     uint64_t *xy_dev, uint64_t *r_dev, uint64_t *acc_dev);
 
 /* ------------------------------------------------------------------ a12/a13: --use_ot
  * Correlated-OT extension behind inner_product_ot_sender / inner_product_ot_recver

@@ -73,6 +73,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->wire_ws_bytes = 0;
 	ctx->opt_tc_max_slices = ctx->opt_tc_chunk_blocks = ctx->opt_tc_min_cols = 0;
 	ctx->opt_ti_threads = 0;
+	ctx->opt_fused_threads = 0;
 	ctx->opt_encode_planes = 0;
 	ctx->opt_encode_async = 1;
 	ctx->prof = false;
@@ -144,6 +145,10 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "ti_threads must be a multiple of 32 in [32,512]");
 		ctx->opt_ti_threads = value;
 	}
+	else if(!strcmp(name, "fused_threads")) {
+		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "fused_threads must be a multiple of 32 in [32,512]");
+		ctx->opt_fused_threads = value;
+	}
 	else if(!strcmp(name, "encode_planes")) ctx->opt_encode_planes = value;
 	else if(!strcmp(name, "encode_async")) ctx->opt_encode_async = value;
 	else return p1_fail("p1_ctx_set_option: unknown option '%s'", name);
@@ -182,7 +187,7 @@ void p1_prof_end(p1_ctx *ctx) {
 }
 
 static const char *const K_NAMES[P1_K_COUNT] = {"encode", "layout", "diag", "gram_imad", "gram_limbs", "gram_tc", "ti_generate",
-	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc", "msg_pack", "msg_unpack", "share_bits", "text"};
+	"party_b_mask", "party_a_step", "party_b_share", "cot_recv", "cot_send", "cot_finish", "misc", "msg_pack", "msg_unpack", "share_bits", "text", "masking_fused"};
 
 extern "C" const char *p1_kernel_class_name(int c) { return c >= 0 && c < P1_K_COUNT ? K_NAMES[c] : NULL; }
 

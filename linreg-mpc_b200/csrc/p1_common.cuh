@@ -30,6 +30,7 @@ struct p1_ctx {
 	void *wire_ws;  size_t wire_ws_bytes;
 	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols;
 	long opt_ti_threads;              // threads per CTA of k_ti_generate (0 = default)
+	long opt_fused_threads;           // threads per CTA of k_masking_fused (0 = default)
 	long opt_encode_async;            // encode through the cp.async pipeline (k_encode_async) when the layout allows
 	long opt_encode_planes;           // p1_encode also writes the digit planes of the tcgen05 Gram (0 = off)
 	// per-kernel-class event timing (p1_ctx_profile)

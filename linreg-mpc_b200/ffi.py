@@ -21,7 +21,7 @@ P1_GRAM_AUTO, P1_GRAM_IMAD, P1_GRAM_TCGEN05 = 0, 1, 2
 # kernel classes of p1_ctx_profile_read (enum in include/p1gpu.h)
 (P1_K_ENCODE, P1_K_LAYOUT, P1_K_DIAG, P1_K_GRAM_IMAD, P1_K_GRAM_LIMBS, P1_K_GRAM_TC, P1_K_TI, P1_K_PARTY_B_MASK,
  P1_K_PARTY_A_STEP, P1_K_PARTY_B_SHARE, P1_K_COT_RECV, P1_K_COT_SEND, P1_K_COT_FINISH, P1_K_MISC, P1_K_MSG_PACK, P1_K_MSG_UNPACK, P1_K_SHARE_BITS,
- P1_K_TEXT, P1_K_COUNT) = range(19)
+ P1_K_TEXT, P1_K_MASKING_FUSED, P1_K_COUNT) = range(20)
 P1_MSG_BAD_HEADER, P1_MSG_BAD_COUNT, P1_MSG_BAD_VARINT = 1, 2, 4
 
 # every symbol include/p1gpu.h declares, with its signature
@@ -61,6 +61,8 @@ SIGNATURES = {
     "p1_party_a_step": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz, c_vp]),
     "p1_party_b_share": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp]),
     "p1_acc_sub_values": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz]),
+    "p1_masking_fused": (c_i, [c_vp, c_cp, c_u64, c_sz, c_sz, c_sz, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_vp,
+                               c_vp, c_vp, c_vp]),
     "p1_cot_sender_new": (c_i, [c_vp, c_cp, c_vp, ctypes.POINTER(c_vp)]),
     "p1_cot_receiver_new": (c_i, [c_vp, c_vp, c_vp, ctypes.POINTER(c_vp)]),
     "p1_cot_free": (None, [c_vp]),

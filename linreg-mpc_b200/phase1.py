@@ -254,8 +254,13 @@ class Phase1Box:
         L.check(L.p1_msg_unpack(ctx, ptr(wr["buf"]), self.wire_stride, ptr(wr["sizes"]), B, self.n_rows, vec, self.ld,
                                 ptr(wr["vals"]), ptr(wr["status"])))
 
-    def cross_pairs_masking(self, ti_key, seeded=False, wire=False, max_pairs=None):
+    def cross_pairs_masking(self, ti_key, seeded=False, wire=False, max_pairs=None, fused=None, keep_masks=False):
         """TI masking protocol for every cross pair (src/phase1.c:257-285 and :148-236).
+        fused (default: whenever neither seeded nor wire is asked for): the whole batch in ONE
+                      persistent kernel (p1_masking_fused) - mask expansion, b's masked column, a's step and
+                      b's share on the same rows, the masks never leave the SM; the two party messages are
+                      written as before.  keep_masks=True also materialises x and y (tests).  fused=False:
+                      the four kernels a deployment with parties on different devices runs.
         seeded=False: the TI materialises x and y once (what the reference ships);
         seeded=True : the TI computes only the values; each provider expands its own
                       mask from (key, q) - same share words.
@@ -265,6 +270,10 @@ class Phase1Box:
         C = self.sched.num_cross if max_pairs is None else min(self.sched.num_cross, int(max_pairs))
         if not C:
             return
+        if fused is None:
+            fused = not seeded and not wire
+        if fused and (seeded or wire):
+            raise ValueError("the fused masking loop hands messages over in HBM: not with seeded / wire")
         self._ensure_bufs()
         if wire:
             self._ensure_wire()
@@ -283,6 +292,11 @@ class Phase1Box:
             sb = c_vp(self.slot_b.data_ptr() + 8 * q0)
             acc = c_vp(self.acc.data_ptr())
             args = (ti_key, q0, B, self.n_total, self.row0, self.n_rows)
+            if fused:
+                L.check(L.p1_masking_fused(ctx, ti_key, q0, B, self.n_total, self.row0, self.data, ca, cb, sa, sb,
+                                           mb, ma, self.ld, xb if keep_masks else None, yb if keep_masks else None,
+                                           xy, r, acc))
+                continue
             if not seeded:
                 L.check(L.p1_ti_generate(ctx, *args, xb, yb, self.ld, xy, r))
             else:
@@ -413,12 +427,12 @@ class Phase1Box:
         self.all_reduce()
         return self.finalize()
 
-    def run_masking(self, X, y, ti_key, seeded=False, wire=False):
+    def run_masking(self, X, y, ti_key, seeded=False, wire=False, fused=None):
         """whole phase 1 with the TI masking protocol; returns every provider's shares"""
         self.reset()
         self.encode(X, y)
         self.local_blocks()
-        self.cross_pairs_masking(ti_key, seeded=seeded, wire=wire)
+        self.cross_pairs_masking(ti_key, seeded=seeded, wire=wire, fused=fused)
         self.all_reduce()
         self.apply_values()
         return self.finalize()

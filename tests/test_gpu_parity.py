@@ -483,6 +483,63 @@ def test_party_kernels_parity(p1lib, oracle, bits):
 
 
 @pytest.mark.parametrize("bits", [64, 32])
+@pytest.mark.parametrize("n_total,row0,n_rows", [(9000, 0, 9000), (9001, 0, 9001), (9003, 0, 9003), (20480, 4096, 8192),
+                                                 (9999, 3333, 6666), (130, 0, 130), (1, 0, 1), (70000, 512, 66000)])
+def test_masking_fused_parity(p1lib, oracle, bits, n_total, row0, n_rows):
+    """the one-kernel masking loop (p1_masking_fused): both party messages, the masks when kept, <x,y>, r
+    and both share sums equal the oracle's TI stream + party algebra (src/phase1.c:173-224,270-278), for
+    every phase of a pair's mask inside the 16-byte AES blocks (odd pairs, odd n, row shards)"""
+    ctx = mkctx(p1lib, bits, bits)
+    rng = np.random.default_rng(80 + n_total)
+    dt = po.word_dtype(bits)
+    d, q0, count = 5, 7, 6
+    Xw = rng.integers(0, 2 ** 63, (n_rows, d), dtype=np.uint64).astype(dt)
+    yw = rng.integers(0, 2 ** 63, n_rows, dtype=np.uint64).astype(dt)
+    data = from_words(p1lib, ctx, Xw, yw)
+    colv = lambda c: yw if c == d else Xw[:, c]
+    ld = (n_rows + 255) // 256 * 256
+    cols_a = np.array([5, 4, 4, 3, 2, 5], np.int32)      # 5 = the target vector
+    cols_b = np.array([0, 1, 2, 0, 1, 3], np.int32)
+    slots_a = np.array([0, 1, 2, 3, 1, 5], np.int64)      # slot 1 is hit twice: accumulation
+    slots_b = np.array([8, 9, 10, 11, 12, 9], np.int64)
+    mask = (1 << bits) - 1
+    for keep in (False, True):
+        bufs = [dev_zeros(p1lib, ctx, count * ld * dt().nbytes) for _ in range(4)]
+        mb, ma, x, y = bufs
+        xy = dev_zeros(p1lib, ctx, 8 * count)
+        r = dev_zeros(p1lib, ctx, 8 * count)
+        acc = dev_zeros(p1lib, ctx, 8 * 16)
+        p1lib.check(p1lib.p1_masking_fused(ctx, po.TI_KEY, q0, count, n_total, row0, data, vp(cols_a), vp(cols_b),
+                                           vp(slots_a), vp(slots_b), mb, ma, ld, x if keep else None, y if keep else None,
+                                           xy, r, acc))
+        mbh, mah = to_host(p1lib, ctx, mb, (count, ld), dt), to_host(p1lib, ctx, ma, (count, ld), dt)
+        xh, yh = to_host(p1lib, ctx, x, (count, ld), dt), to_host(p1lib, ctx, y, (count, ld), dt)
+        xyh, rh = to_host(p1lib, ctx, xy, count, np.uint64), to_host(p1lib, ctx, r, count, np.uint64)
+        acch = to_host(p1lib, ctx, acc, 16, np.uint64)
+        want = np.zeros(16, np.uint64)
+        for p in range(count):
+            xo, yo, va, vb = oracle.ti_pair(po.TI_KEY, q0 + p, n_total, bits)
+            xo, yo = xo[row0:row0 + n_rows], yo[row0:row0 + n_rows]
+            a, b = colv(cols_a[p]), colv(cols_b[p])
+            assert np.array_equal(mbh[p, :n_rows], b + xo), p
+            assert np.array_equal(mah[p, :n_rows], a - yo), p
+            assert not mbh[p, n_rows:].any() and not mah[p, n_rows:].any()     # padding untouched
+            if keep:
+                assert np.array_equal(xh[p, :n_rows], xo) and np.array_equal(yh[p, :n_rows], yo)
+            else:
+                assert not xh.any() and not yh.any()
+            assert int(rh[p]) == vb
+            assert int(xyh[p]) & mask == oracle.dot(xo, yo, bits)
+            want[slots_a[p]] += np.uint64(oracle.dot(b + xo, yo, bits))
+            want[slots_b[p]] += np.uint64(oracle.dot(a - yo, b, bits))
+        assert np.array_equal(acch & np.uint64(mask), want & np.uint64(mask))
+        for p_ in bufs + [xy, r, acc]:
+            p1lib.check(p1lib.p1_dev_free(ctx, p_))
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
 @pytest.mark.parametrize("n", [64, 37, 515])
 def test_cot_inner_product_parity(p1lib, oracle, bits, n):
     """one OT-based inner product: both shares and both wire messages equal the oracle's"""
@@ -535,8 +592,10 @@ def test_whole_phase1_matches_reference_golden(p1lib, golden):
         if c["use_ot"]:
             got = box.run_ot(c["X"], c["y"], golden["ot_key"])
         else:
-            got = box.run_masking(c["X"], c["y"], golden["ti_key"])
+            got = box.run_masking(c["X"], c["y"], golden["ti_key"])               # one-kernel masking loop
             assert np.array_equal(got, c["shares"]), ("masking", c["instance"], c["bits_p1"], c["bits_p2"])
+            got = box.run_masking(c["X"], c["y"], golden["ti_key"], fused=False)  # TI / party kernels one by one
+            assert np.array_equal(got, c["shares"]), ("masking, split kernels", c["instance"], c["bits_p1"], c["bits_p2"])
             got = box.run_masking(c["X"], c["y"], golden["ti_key"], seeded=True)  # CSP-seeded masks: same words
         assert np.array_equal(got, c["shares"]), (c["instance"], c["bits_p1"], c["bits_p2"], c["use_ot"])
         box.close()
@@ -552,6 +611,7 @@ def test_whole_phase1_random_instance(p1lib, oracle, b1, b2, prec, prec2):
     got = box.run_masking(X, y, po.TI_KEY)
     assert np.array_equal(got, want)
     assert box.launches() > 0
+    assert np.array_equal(box.run_masking(X, y, po.TI_KEY, fused=False), want)
     # same run with every message serialised and parsed on the GPU, and with provider-expanded masks
     assert np.array_equal(box.run_masking(X, y, po.TI_KEY, wire=True), want)
     assert np.array_equal(box.run_masking(X, y, po.TI_KEY, seeded=True), want)
