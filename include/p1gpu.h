@@ -266,8 +266,24 @@ int p1_cot_receiver_extend(p1_ctx *ctx, p1_cot *r, const p1_data *data, int32_t 
 int p1_cot_sender_step(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col,
                        size_t n_total, size_t row0, const void *u_dev,
                        void *c_dev, uint64_t *acc_dev, int64_t slot);
+/* Moves the session cursor past `count` inner products of n_total rows without computing them:
+ * two sessions built from the same base-OT outputs can then take alternate inner products of
+ * one peer session on two streams (each receiver keeps its own pads), every one at the cursor
+ * the single-session order gives it. */
+int p1_cot_advance(p1_cot *session, size_t n_total, size_t count);
+/* Sets the cursor outright (PRG block, OT counter): resuming a session, and the tests that start
+ * beyond 2^32 blocks. */
+int p1_cot_set_cursor(p1_cot *session, uint64_t prg_block, uint64_t ot_counter);
 /* receiver, second half: adds +sum(dest) into acc_dev[slot] */
 int p1_cot_receiver_finish(p1_ctx *ctx, p1_cot *r, const void *c_dev, uint64_t *acc_dev, int64_t slot);
+
+/* Dense int8 tensor-core rate of this GPU, measured (the roofline denominator of the tcgen05 Gram;
+ * MEASURED_PEAKS.json has no int8 entry).  One CTA per SM issues back-to-back
+ * tcgen05.mma cta_group::1 kind::i8 instructions of shape M = 128, N = n_cols, K = 32 on operands that
+ * stay in shared memory (no TMA, no epilogue) for at least min_ms milliseconds; *tops = executed int8
+ * ops (2 per MAC) / time / 1e12.  n_cols: multiple of 16 in [16, 256] (192 = the Gram kernel's
+ * instruction for 3-digit words). */
+int p1_probe_tensor_i8(p1_ctx *ctx, int n_cols, double min_ms, double *tops, double *ms, uint64_t *ops);
 
 /* ------------------------------------------------------------------ a14: finalize
  * Tail of run_party (src/phase1.c:605-641).  `acc` (host or device, p1_acc_len(d)

@@ -24,7 +24,7 @@ struct p1_cot {
 	size_t n_rows;
 };
 
-#define COT_GROUPS 8
+#define COT_GROUPS 4
 #define COT_THREADS (128 * COT_GROUPS)
 
 struct CotParams {
@@ -47,6 +47,51 @@ __device__ __forceinline__ void group_sync(int g) {
 	asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(128) : "memory");
 }
 
+// A thread keeps the CTR key of ITS column (thread t <-> column t for the whole launch) in
+// registers: round keys 8..43, rk[3], and round 1 of the counter block 0^64 || BE32(hi) || BE32(lo)
+// without the four lookups that depend on lo (as AesCtrKey does for the grid-wide TI key).  A PRG
+// block then costs 4 + 144 shared-memory lookups and no round-key loads (was 160 + 44).
+struct AesRegCtrKey {
+	uint32_t hi, rk3, c1[4], rk[36];
+};
+struct AesRegAcc {
+	const AesRegCtrKey &R;
+	__device__ __forceinline__ AesRegAcc(const AesRegCtrKey &r) : R(r) {}
+	__device__ __forceinline__ uint32_t operator()(int i) const { return R.rk[i - 8]; }
+};
+__device__ __forceinline__ void aes_regkey_init(const AesSmemKey &k, uint32_t lb, uint32_t hi, AesRegCtrKey &R) {
+	R.hi = hi;
+	R.rk3 = k(3);
+#pragma unroll
+	for(int i = 0; i < 36; i++) R.rk[i] = k(8 + i);
+	const uint32_t s0 = k(0), s1 = k(1), s2 = __byte_perm(hi, 0, 0x0123) ^ k(2);
+	R.c1[0] = aes_lk<0, 0>(s0, lb) ^ aes_lk<1, 1>(s1, lb) ^ aes_lk<2, 2>(s2, lb) ^ k(4);
+	R.c1[1] = aes_lk<0, 0>(s1, lb) ^ aes_lk<1, 1>(s2, lb) ^ aes_lk<3, 3>(s0, lb) ^ k(5);
+	R.c1[2] = aes_lk<0, 0>(s2, lb) ^ aes_lk<2, 2>(s0, lb) ^ aes_lk<3, 3>(s1, lb) ^ k(6);
+	R.c1[3] = aes_lk<1, 1>(s0, lb) ^ aes_lk<2, 2>(s1, lb) ^ aes_lk<3, 3>(s2, lb) ^ k(7);
+}
+// keystream block `block` (block >> 32 == R.hi)
+__device__ __forceinline__ void aes_ctr_block_r(const AesRegCtrKey &R, uint32_t lb, uint32_t lo, uint32_t s[4]) {
+	const uint32_t s3 = __byte_perm(lo, 0, 0x0123) ^ R.rk3;
+	const uint32_t t0 = R.c1[0] ^ aes_lk<3, 3>(s3, lb);
+	const uint32_t t1 = R.c1[1] ^ aes_lk<2, 2>(s3, lb);
+	const uint32_t t2 = R.c1[2] ^ aes_lk<1, 1>(s3, lb);
+	const uint32_t t3 = R.c1[3] ^ aes_lk<0, 0>(s3, lb);
+	aes_rounds_to_10<2>(AesRegAcc(R), lb, t0, t1, t2, t3, s);
+}
+
+// 32x32 bit-matrix transpose across a warp: lane r holds row r, returns row r of the transpose
+// (five butterfly steps: swap the off-diagonal j x j blocks of every 2j x 2j block)
+__device__ __forceinline__ uint32_t cot_transpose32(uint32_t x, uint32_t lane) {
+#pragma unroll
+	for(int j = 16; j; j >>= 1) {
+		const uint32_t m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;
+		const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+		x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y << j) & ~m));
+	}
+	return x;
+}
+
 // ROLE 0: receiver extend, ROLE 1: sender step
 template <typename W, int ROLE>
 __global__ void __launch_bounds__(COT_THREADS, 1) k_cot_tiles(const CotParams P) {
@@ -64,35 +109,34 @@ __global__ void __launch_bounds__(COT_THREADS, 1) k_cot_tiles(const CotParams P)
 	const uint32_t lb = aes_lane_base(sT, (uint32_t) lane);
 	uint32_t *myR = sR + g * 128 * 5;
 	const bool dbit = ROLE == 1 && ((P.delta[t >> 5] >> (t & 31)) & 1);
+	const AesSmemKey k0s(sK, 128, t), k1s(sK + 44 * 128, 128, t);
+	AesRegCtrKey K0, K1;
+	aes_regkey_init(k0s, lb, (uint32_t) (P.ctr0 >> 32), K0);
+	if(ROLE == 0) aes_regkey_init(k1s, lb, (uint32_t) (P.ctr0 >> 32), K1);
 	uint64_t dot = 0;
 	for(uint64_t tile = (uint64_t) blockIdx.x * COT_GROUPS + g; tile < P.tiles; tile += (uint64_t) gridDim.x * COT_GROUPS) {
 		// ---- column phase: thread t = column t of the kappa x m matrix
+		const uint64_t blk = P.ctr0 + tile;
+		if((uint32_t) (blk >> 32) != K0.hi) {                                                       // uniform over the group
+			aes_regkey_init(k0s, lb, (uint32_t) (blk >> 32), K0);
+			if(ROLE == 0) aes_regkey_init(k1s, lb, (uint32_t) (blk >> 32), K1);
+		}
 		uint32_t a[4];
-		aes_ctr_block_k(AesSmemKey(sK, 128, t), lb, P.ctr0 + tile, a);
+		aes_ctr_block_r(K0, lb, (uint32_t) blk, a);
 		uint4 *up = reinterpret_cast<uint4 *>((char *) P.u + tile * 2048) + t;
 		if(ROLE == 0) {
 			uint32_t b[4];
-			aes_ctr_block_k(AesSmemKey(sK + 44 * 128, 128, t), lb, P.ctr0 + tile, b);
+			aes_ctr_block_r(K1, lb, (uint32_t) blk, b);
 			const uint4 ch = *(reinterpret_cast<const uint4 *>(P.col) + tile); // 128 choice bits = 16 bytes of the column
 			*up = make_uint4(a[0] ^ b[0] ^ ch.x, a[1] ^ b[1] ^ ch.y, a[2] ^ b[2] ^ ch.z, a[3] ^ b[3] ^ ch.w);
 		} else if(dbit) {
 			const uint4 uv = *up;
 			a[0] ^= uv.x; a[1] ^= uv.y; a[2] ^= uv.z; a[3] ^= uv.w;
 		}
-		// ---- 128x128 bit transpose: ballot over the 32 columns of this warp
-		uint32_t keep[4];
+		// ---- 128x128 bit transpose: four 32x32 butterflies per warp (word b of the warp's 32 columns ->
+		// word wq of rows 32b .. 32b+31), then the rows are gathered through shared memory
 #pragma unroll
-		for(int b = 0; b < 4; b++) {
-			uint32_t mine = 0;
-#pragma unroll
-			for(int bit = 0; bit < 32; bit++) {
-				uint32_t v = __ballot_sync(0xffffffffu, (a[b] >> bit) & 1);
-				if(lane == bit) mine = v;
-			}
-			keep[b] = mine;
-		}
-#pragma unroll
-		for(int b = 0; b < 4; b++) myR[(32 * b + lane) * 5 + wq] = keep[b];
+		for(int b = 0; b < 4; b++) myR[(32 * b + lane) * 5 + wq] = cot_transpose32(a[b], (uint32_t) lane);
 		group_sync(g);
 		// ---- row phase: thread t = OT t of the tile
 		uint32_t x0 = myR[t * 5 + 0], x1 = myR[t * 5 + 1], x2 = myR[t * 5 + 2], x3 = myR[t * 5 + 3];
@@ -261,7 +305,6 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 		s->col_ptr = P.col;
 		s->n_rows = data->n;
 	}
-	constexpr int NK = ROLE == 0 ? 2 : 1;
 	size_t smem = AES_SMEM_BYTES + COT_GROUPS * 128 * 5 * sizeof(uint32_t);  // key schedules live in the gap below the tables
 	static_assert(2 * 44 * 128 * 4 <= AES_SMEM_GAP, "key schedules must fit below the AES tables");
 	uint64_t grid = (P.tiles + COT_GROUPS - 1) / COT_GROUPS;
@@ -284,6 +327,21 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 	size_t tiles_total = cot_tiles(s->bits, n_total);
 	s->pos += tiles_total;
 	s->ot_base += 128 * (uint64_t) tiles_total;
+	return 0;
+}
+
+extern "C" int p1_cot_advance(p1_cot *s, size_t n_total, size_t count) {
+	P1_CHECK(s, "p1_cot_advance: null session");
+	const size_t tiles_total = cot_tiles(s->bits, n_total);
+	s->pos += (uint64_t) count * tiles_total;
+	s->ot_base += 128 * (uint64_t) count * tiles_total;
+	return 0;
+}
+
+extern "C" int p1_cot_set_cursor(p1_cot *s, uint64_t prg_block, uint64_t ot_counter) {
+	P1_CHECK(s, "p1_cot_set_cursor: null session");
+	s->pos = prg_block;
+	s->ot_base = ot_counter;
 	return 0;
 }
 

@@ -136,10 +136,9 @@ __device__ __forceinline__ void fu_words(FuPair<W> &S, int64_t ob, const uint32_
 template <typename W, int HW>
 __device__ __forceinline__ void fu_full(FuPair<W> &S, int64_t o, const uint32_t xs[4], const uint32_t ys[4],
 	uint32_t cx[4], uint32_t cy[4], bool &carry, bool last, uint32_t lane) {
-	if(HW == 0) {
+	if constexpr(HW == 0) {
 		fu_line<W>(S, (uint64_t) o / sizeof(W), xs, ys);
-		return;
-	}
+	} else {
 	uint32_t lx[4], ly[4];
 #pragma unroll
 	for(int i = 0; i < 4; i++) {
@@ -159,6 +158,7 @@ __device__ __forceinline__ void fu_full(FuPair<W> &S, int64_t o, const uint32_t 
 	else fu_words<W>(S, o, xs, ys, 0, HW);                      // head of the run: no tail to join
 	if(last && lane == 31) fu_words<W>(S, o, xs, ys, HW, 4);   // end of the run: nobody takes this tail
 	carry = true;
+	}
 }
 
 template <typename W, bool ALIGNED>

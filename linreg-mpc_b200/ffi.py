@@ -70,7 +70,10 @@ SIGNATURES = {
     "p1_cot_c_bytes": (c_sz, [c_vp, c_sz]),
     "p1_cot_receiver_extend": (c_i, [c_vp, c_vp, c_vp, c_i32, c_sz, c_sz, c_vp]),
     "p1_cot_sender_step": (c_i, [c_vp, c_vp, c_vp, c_i32, c_sz, c_sz, c_vp, c_vp, c_vp, c_i64]),
+    "p1_cot_advance": (c_i, [c_vp, c_sz, c_sz]),
+    "p1_cot_set_cursor": (c_i, [c_vp, c_u64, c_u64]),
     "p1_cot_receiver_finish": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "p1_probe_tensor_i8": (c_i, [c_vp, c_i, c_d, ctypes.POINTER(c_d), ctypes.POINTER(c_d), ctypes.POINTER(c_u64)]),
     "p1_finalize": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_i, c_i, c_d, c_vp, c_vp,
                           ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
     "p1_msg_max_bytes": (c_sz, [c_vp, c_sz]),

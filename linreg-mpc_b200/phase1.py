@@ -347,6 +347,12 @@ class Phase1Box:
             return step(np.zeros(hi - lo, dtype=np.float64))
         return chain_in_rank_order(step, hi - lo, self.group, self.dev)
 
+    def accumulators(self):
+        """host copy of every provider's uint64 accumulator, [num_dp, p1_acc_len(d)] (the share words before
+        the diagonal / 64->32 tail of p1_finalize; combined over ranks once all_reduce() has run)"""
+        self.sync()
+        return self.acc.cpu().numpy().view(np.uint64).reshape(self.sched.num_dp, self.acc_len).copy()
+
     def finalize(self):
         """tail of run_party for every provider (src/phase1.c:605-641): returns
         shares[num_dp, d(d+1)/2 + d] as ufixed_t widened to uint64."""
@@ -376,47 +382,78 @@ class Phase1Box:
         return out
 
     # ------------------------------------------------------------------
-    def cross_pairs_ot(self, ot_key):
-        """--use_ot aggregation (src/phase1.c:386-449): one OT-extension session per pair
-        of providers, sender/receiver by the parity rule of :392, inner products in the
-        loop order of :404-438.  The base-OT outputs (seeds, Delta) are inputs."""
-        S, L, ctx, t = self.sched, self.lib, self.ctxs[0], self.torch
-        P, d = S.num_dp, self.d
-        u_bytes = int(L.p1_cot_u_bytes(ctx, self.n_rows))
-        c_bytes = int(L.p1_cot_c_bytes(ctx, self.n_rows))
-        ubuf = t.empty(u_bytes, dtype=t.uint8, device=self.dev)
-        cbuf = t.empty(c_bytes, dtype=t.uint8, device=self.dev)
-        t.cuda.current_stream(self.dev).synchronize()
-        acc = self.acc.data_ptr()
-
-        def inner(snd, rcv, ps, pr, col_s, col_r, slot):
-            L.check(L.p1_cot_receiver_extend(ctx, rcv, self.data, col_r, self.n_total, self.row0, ptr(ubuf)))
-            L.check(L.p1_cot_sender_step(ctx, snd, self.data, col_s, self.n_total, self.row0, ptr(ubuf), ptr(cbuf),
-                                         c_vp(acc), ps * self.acc_len + slot))
-            L.check(L.p1_cot_receiver_finish(ctx, rcv, ptr(cbuf), c_vp(acc), pr * self.acc_len + slot))
-
+    def ot_schedule(self):
+        """The inner products of the --use_ot aggregation in the order of src/phase1.c:386-438: for every
+        pair of providers (me < peer) one session, sender by the parity rule of :392; inside a session
+        sender columns x receiver columns (:404-414), then (i, target) when the receiver is the last
+        provider (:415-424) and (target, j) when the sender is (:426-438).
+        Yields (sender provider, receiver provider, [(col_s, col_r, slot), ...])."""
+        S, P, d = self.sched, self.sched.num_dp, self.d
         for me in range(P):
             for peer in range(me + 1, P):
                 me_sends = ((me % 2 == peer % 2) == (me < peer))
                 ps, pr = (me, peer) if me_sends else (peer, me)
-                seeds0, seeds1, delta = derive_cot_session(ot_key, ps + 2, pr + 2)
-                chosen = np.where(_bits128(delta)[:, None], seeds1, seeds0)
-                snd, rcv = c_vp(), c_vp()
-                L.check(L.p1_cot_sender_new(ctx, delta.tobytes(), ptr(np.ascontiguousarray(chosen)), ctypes.byref(snd)))
-                L.check(L.p1_cot_receiver_new(ctx, ptr(seeds0), ptr(seeds1), ctypes.byref(rcv)))
                 i_lo, i_hi = S.col_range(ps)
                 j_lo, j_hi = S.col_range(pr)
+                items = []
                 for i in range(i_lo, i_hi):
-                    for j in range(j_lo, j_hi):
-                        inner(snd, rcv, ps, pr, i, j, int(idx(np.int64(i), np.int64(j))))
+                    items += [(i, j, int(idx(np.int64(i), np.int64(j)))) for j in range(j_lo, j_hi)]
                     if pr == P - 1:
-                        inner(snd, rcv, ps, pr, i, d, S.nA + i)          # (i, target) -> share_b[i]
+                        items.append((i, d, S.nA + i))          # (i, target) -> share_b[i]
                 if ps == P - 1:
-                    for j in range(j_lo, j_hi):
-                        inner(snd, rcv, ps, pr, d, j, S.nA + j)          # (target, j) -> share_b[j]
+                    items += [(d, j, S.nA + j) for j in range(j_lo, j_hi)]   # (target, j) -> share_b[j]
+                yield ps, pr, items
+
+    def cross_pairs_ot(self, ot_key, max_pairs=None):
+        """--use_ot aggregation (src/phase1.c:386-449).  The base-OT outputs (seeds, Delta) are inputs.
+        Inner products of a session alternate over the box's pipes (streams): every pipe holds its own pair
+        of session objects built from the same seeds and skips the inner products of the others
+        (p1_cot_advance), so each one runs at the cursor the reference's single loop gives it while the
+        receiver's finish of one overlaps the next one's extension.  max_pairs: stop after that many inner
+        products (bench samples).  Returns the number of inner products executed."""
+        L, t = self.lib, self.torch
+        ctx0 = self.ctxs[0]
+        npipe = len(self.ctxs)
+        u_bytes = int(L.p1_cot_u_bytes(ctx0, self.n_rows))
+        c_bytes = int(L.p1_cot_c_bytes(ctx0, self.n_rows))
+        if getattr(self, "_ot_bufs", None) is None:
+            self._ot_bufs = [(t.empty(u_bytes, dtype=t.uint8, device=self.dev), t.empty(c_bytes, dtype=t.uint8, device=self.dev))
+                             for _ in self.ctxs]
+            t.cuda.current_stream(self.dev).synchronize()
+        acc = self.acc.data_ptr()
+        done = 0
+        self._fan_out()
+        for ps, pr, items in self.ot_schedule():
+            if max_pairs is not None and done >= max_pairs:
+                break
+            seeds0, seeds1, delta = derive_cot_session(ot_key, ps + 2, pr + 2)
+            chosen = np.ascontiguousarray(np.where(_bits128(delta)[:, None], seeds1, seeds0))
+            sess = []
+            for ctx in self.ctxs:
+                snd, rcv = c_vp(), c_vp()
+                L.check(L.p1_cot_sender_new(ctx, delta.tobytes(), ptr(chosen), ctypes.byref(snd)))
+                L.check(L.p1_cot_receiver_new(ctx, ptr(seeds0), ptr(seeds1), ctypes.byref(rcv)))
+                sess.append((snd, rcv))
+            for k, (col_s, col_r, slot) in enumerate(items):
+                if max_pairs is not None and done >= max_pairs:
+                    break
+                pipe = k % npipe
+                ctx, (snd, rcv), (ubuf, cbuf) = self.ctxs[pipe], sess[pipe], self._ot_bufs[pipe]
+                L.check(L.p1_cot_receiver_extend(ctx, rcv, self.data, col_r, self.n_total, self.row0, ptr(ubuf)))
+                L.check(L.p1_cot_sender_step(ctx, snd, self.data, col_s, self.n_total, self.row0, ptr(ubuf), ptr(cbuf),
+                                             c_vp(acc), ps * self.acc_len + slot))
+                L.check(L.p1_cot_receiver_finish(ctx, rcv, ptr(cbuf), c_vp(acc), pr * self.acc_len + slot))
+                for q, (s2, r2) in enumerate(sess):
+                    if q != pipe:
+                        L.check(L.p1_cot_advance(s2, self.n_total, 1))
+                        L.check(L.p1_cot_advance(r2, self.n_total, 1))
+                done += 1
+            for ctx, (snd, rcv) in zip(self.ctxs, sess):
                 L.check(L.p1_ctx_sync(ctx))
                 L.p1_cot_free(snd)
                 L.p1_cot_free(rcv)
+        self._fan_in()
+        return done
 
     def run_ot(self, X, y, ot_key):
         """whole phase 1 with the OT-based aggregation; returns every provider's shares"""

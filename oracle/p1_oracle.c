@@ -227,6 +227,11 @@ p1o_ot_session *p1o_ot_session_new(const uint8_t ot_key[16], int sender_party, i
 void p1o_ot_session_free(p1o_ot_session *ss) {
 	free(ss);
 }
+/* resume a session at a given PRG block / OT counter (tests of long sessions) */
+void p1o_ot_session_set_cursor(p1o_ot_session *ss, uint64_t pos, uint64_t ot_base) {
+	ss->s.pos = ss->r.pos = pos;
+	ss->s.ot_base = ss->r.ot_base = ot_base;
+}
 
 /* One inner product <xs, xr>: sender holds xs (inner_product_ot_sender :53-72), receiver
  * holds xr (inner_product_ot_recver :74-96).  OT index ni = k*W + bit (:45-46); choice

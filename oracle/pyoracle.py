@@ -85,6 +85,7 @@ class Oracle:
         L.p1o_ot_session_new.argtypes = [c_u8p, c_i, c_i]
         L.p1o_ot_session_new.restype = c_vp
         L.p1o_ot_session_free.argtypes = [c_vp]
+        L.p1o_ot_session_set_cursor.argtypes = [c_vp, c_u64, c_u64]
         L.p1o_ot_inner_product.argtypes = [c_vp, c_vp, c_sz, c_vp, c_sz, c_sz, c_i, c_vp, c_vp, c_vp, c_vp]
         L.p1o_downconvert.argtypes = [c_u64, c_i, c_i]
         L.p1o_downconvert.restype = c_u64

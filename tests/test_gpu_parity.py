@@ -577,6 +577,78 @@ def test_cot_inner_product_parity(p1lib, oracle, bits, n):
     p1lib.p1_ctx_destroy(ctx)
 
 
+@pytest.mark.parametrize("bits", [64, 32])
+def test_cot_row_shards_and_long_session(p1lib, oracle, bits):
+    """OT inner products over row shards with row0 > 0 (as the ranks of a row-sharded box hold them) on a
+    session whose PRG block cursor and OT counter cross 2^32 inside the inner product: every shard's U / C
+    bytes are the slices of the oracle's wire messages and the shard sums add up to the oracle's shares;
+    a second session built from the same seeds and moved with p1_cot_advance lands on the same words"""
+    from linreg_mpc_b200 import phase1
+    ctx = mkctx(p1lib, bits, bits)
+    rng = np.random.default_rng(12)
+    dt = po.word_dtype(bits)
+    w = bits // 8
+    n = 3000
+    per_tile = 128 // bits
+    Xw = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64).astype(dt) * dt(5)
+    cuts = [0, 1024, 1024 + 768, n]            # multiples of 256 rows, the last shard ragged
+    shards = [from_words(p1lib, ctx, np.ascontiguousarray(Xw[a:b]), None) for a, b in zip(cuts[:-1], cuts[1:])]
+    s0, s1, delta = phase1.derive_cot_session(po.OT_KEY, 3, 2)
+    chosen = np.ascontiguousarray(np.where(phase1._bits128(delta)[:, None], s1, s0))
+    tiles_total = (n * bits + 127) // 128
+    pos0, base0 = 2 ** 32 - tiles_total // 2, 2 ** 32 - 777      # both cross 2^32 inside the first inner product
+    ss = oracle.lib.p1o_ot_session_new(po.OT_KEY, 3, 2)
+    oracle.lib.p1o_ot_session_set_cursor(ss, pos0, base0)
+    mask = (1 << bits) - 1
+
+    def sessions(skip):
+        snd, rcv = c_vp(), c_vp()
+        p1lib.check(p1lib.p1_cot_sender_new(ctx, delta.tobytes(), vp(chosen), ctypes.byref(snd)))
+        p1lib.check(p1lib.p1_cot_receiver_new(ctx, vp(s0), vp(s1), ctypes.byref(rcv)))
+        for s_ in (snd, rcv):
+            p1lib.check(p1lib.p1_cot_set_cursor(s_, pos0, base0))
+            p1lib.check(p1lib.p1_cot_advance(s_, n, skip))
+        return snd, rcv
+
+    per_shard = [sessions(0) for _ in shards]      # every rank has its own session objects, all in step
+    acc = dev_zeros(p1lib, ctx, 8 * 4)
+    want = []
+    for rep in range(2):
+        os_, or_, uo, co = oracle.ot_inner_product(ss, Xw[:, 0], Xw[:, 1], bits, want_wire=True)
+        want.append((os_, or_))
+        p1lib.check(p1lib.p1_dev_zero(ctx, acc, 32))
+        for (a, b), data, (snd, rcv) in zip(zip(cuts[:-1], cuts[1:]), shards, per_shard):
+            rows = b - a
+            ub, cb = int(p1lib.p1_cot_u_bytes(ctx, rows)), int(p1lib.p1_cot_c_bytes(ctx, rows))
+            u = dev_zeros(p1lib, ctx, ub); c = dev_zeros(p1lib, ctx, cb)
+            p1lib.check(p1lib.p1_cot_receiver_extend(ctx, rcv, data, 1, n, a, u))
+            p1lib.check(p1lib.p1_cot_sender_step(ctx, snd, data, 0, n, a, u, c, acc, 0))
+            p1lib.check(p1lib.p1_cot_receiver_finish(ctx, rcv, c, acc, 1))
+            t0 = a // per_tile
+            assert np.array_equal(to_host(p1lib, ctx, u, ub, np.uint8), uo[2048 * t0:2048 * t0 + ub])
+            assert np.array_equal(to_host(p1lib, ctx, c, cb, np.uint8)[:rows * bits * w], co[a * bits * w:b * bits * w])
+            p1lib.check(p1lib.p1_dev_free(ctx, u)); p1lib.check(p1lib.p1_dev_free(ctx, c))
+        got = to_host(p1lib, ctx, acc, 2, np.uint64)
+        assert int(got[0]) & mask == os_ and int(got[1]) & mask == or_, rep
+    # a session that skipped the first inner product computes the second one identically
+    snd, rcv = sessions(1)
+    full = from_words(p1lib, ctx, Xw, None)
+    ub, cb = int(p1lib.p1_cot_u_bytes(ctx, n)), int(p1lib.p1_cot_c_bytes(ctx, n))
+    u = dev_zeros(p1lib, ctx, ub); c = dev_zeros(p1lib, ctx, cb)
+    p1lib.check(p1lib.p1_dev_zero(ctx, acc, 32))
+    p1lib.check(p1lib.p1_cot_receiver_extend(ctx, rcv, full, 1, n, 0, u))
+    p1lib.check(p1lib.p1_cot_sender_step(ctx, snd, full, 0, n, 0, u, c, acc, 0))
+    p1lib.check(p1lib.p1_cot_receiver_finish(ctx, rcv, c, acc, 1))
+    got = to_host(p1lib, ctx, acc, 2, np.uint64)
+    assert (int(got[0]) & mask, int(got[1]) & mask) == want[1]
+    for s_ in [snd, rcv] + [x for pr in per_shard for x in pr]:
+        p1lib.p1_cot_free(s_)
+    oracle.lib.p1o_ot_session_free(ss)
+    for dd in shards + [full]:
+        p1lib.p1_data_free(dd)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 # ---------------------------------------------------------------------------
 def _box(p1lib, c, **kw):
     from linreg_mpc_b200 import phase1
