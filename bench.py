@@ -3,14 +3,20 @@
 
   python bench.py --gpus N --steps K --warmup W            (own arm; torchrun for N > 1)
   python bench.py --impl reference --gpus N --steps K --warmup W
+  python bench.py --workload cfg3 --aggregation ot --ot-pairs 1000     (BASELINE config 3 as written: --use_ot)
+  python bench.py --workload cfg4|cfg5|gram|cfg2|cfg4p5|cfg5p20 ...
 
 One "step" = one whole phase-1 pass over the synthetic instance: fixed-point encode of the
-shard's rows, local Gram blocks, every cross pair of the TI-masking protocol (mask
-expansion, both parties' mask/share kernels), the ring all-reduce over row shards and the
-finalize tail.  Rows are sharded over the N ranks (total work fixed: strong scaling).
-`value` times the step with X, y resident in HBM as doubles; `e2e` times the same step
-through the same calls from pinned HOST buffers, with the device->host read of the shares.
-The CPU legs (cpu_baseline, --impl reference) are the only places that touch oracle/.
+shard's rows, local Gram blocks, every cross pair of the aggregation (TI masking: the fused
+masking loop - mask expansion and both parties' steps; --use_ot: the correlated-OT
+extension), the ring all-reduce over row shards and the finalize tail.  Rows are sharded
+over the N ranks (total work fixed: strong scaling).  `value` times the step with X, y
+resident in HBM as doubles; `e2e` times the same step through the same calls from pinned
+HOST buffers, with the device->host read of the shares.  `check` (outside the timed region,
+every N) proves the shares of the timed configuration: sum invariant on all words against an
+independent one-provider Gram, sampled words against the CPU oracle.
+The CPU legs (cpu_baseline, --impl reference, the oracle inside `check`) are the only places
+that touch oracle/.
 """
 import argparse
 import ctypes
@@ -20,6 +26,7 @@ import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 import numpy as np
@@ -58,50 +65,87 @@ def workload_config(name, wl, aggregation):
 # ----------------------------------------------------------------------------- clocks
 
 class ClockSampler:
+    """SM clock / throttle reasons while the GPU is under load: NVML polled from a thread every ~10 ms
+    (a 200 ms nvidia-smi loop sees nothing of a 15 ms timed region); nvidia-smi as the fallback."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.path = tempfile.mktemp(prefix="clocks_", suffix=".csv")
-        self.proc = None
+    def __init__(self, gpu_index, period_s=0.01):
+        self.sm, self.power, self.reasons, self.smax = [], [], set(), None
+        self.proc = self.thread = None
+        self.stop_flag = False
         try:
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=self.f, stderr=subprocess.DEVNULL)
-        except OSError:
-            self.proc = None
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[gpu_index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else gpu_index
+            h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.smax = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            names = {nv.nvmlClocksEventReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksEventReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksEventReasonSwPowerCap: "sw_power_cap"}
+
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        for bit, nm in names.items():
+                            if r & bit:
+                                self.reasons.add(nm)
+                        self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                    except Exception:
+                        pass
+                    time.sleep(period_s)
+            self.thread = threading.Thread(target=loop, daemon=True)
+            self.thread.start()
+            self.how = "nvml, %d ms" % int(period_s * 1000)
+        except Exception:
+            self.thread = None
+            self.how = "nvidia-smi -lms 100"
+            self.path = tempfile.mktemp(prefix="clocks_", suffix=".csv")
+            try:
+                self.f = open(self.path, "w")
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
+                                              "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+            except OSError:
+                self.proc = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        self.f.close()
-        sm, smax, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        with open(self.path) as f:
-            for line in f:
-                t = [x.strip() for x in line.split(",")]
-                if len(t) < 8:
-                    continue
-                try:
-                    sm.append(float(t[1]))
-                    smax.append(float(t[2]))
-                except ValueError:
-                    continue
-                for nm, v in zip(names, t[4:8]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-        os.unlink(self.path)
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(smax)), samples=len(sm))
-        out["reasons"] = sorted(reasons)
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "how": self.how}
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+        elif self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.f.close()
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            smax = []
+            with open(self.path) as f:
+                for line in f:
+                    t = [x.strip() for x in line.split(",")]
+                    if len(t) < 8:
+                        continue
+                    try:
+                        self.sm.append(float(t[1]))
+                        smax.append(float(t[2]))
+                        self.power.append(float(t[3]))
+                    except ValueError:
+                        continue
+                    for nm, v in zip(names, t[4:8]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(nm)
+            os.unlink(self.path)
+            self.smax = max(smax) if smax else None
+        if self.sm:
+            out.update(sm_mhz=float(np.median(self.sm)), sm_min_mhz=float(min(self.sm)), sm_max_mhz=self.smax, samples=len(self.sm))
+        if self.power:
+            out["power_w_max"] = float(max(self.power))
+        out["reasons"] = sorted(self.reasons)
         return out
 
 
@@ -116,13 +160,14 @@ class ReferenceSample:
     """The reference's own phase1.c (oracle/_ref, compiled unmodified against shims) on a
     bounded sample of the workload: same n as the workload when it fits, few columns."""
 
-    def __init__(self, wl, d_sample, n_sample=None):
+    def __init__(self, wl, d_sample, n_sample=None, use_ot=False):
         from oracle import pyoracle as po
         self.po = po
         self.p = min(wl["p"], d_sample)
         self.n = int(n_sample or min(wl["n"], 1_000_000))
         self.d = d_sample
         self.wl = wl
+        self.use_ot = use_ot
         self.cs = even_col_start(self.d, self.p)
         kind = "reference" if po.RefLib.available(wl["bits_p1"], wl["bits_p2"]) else "port"
         self.kind = kind
@@ -139,28 +184,33 @@ class ReferenceSample:
             self.orc.write_instance(self.path, X, y, self.cs)
             self.ref = po.RefLib(wl["bits_p1"], wl["bits_p2"])
             _, _, self.parse_s = self.ref.read_inputs(self.path, self.n, self.d, wl["precision"])
-        self.macs = ring_macs(self.n, self.d, self.cs)
-        self.threads = self.p + 1 if kind == "reference" else (os.cpu_count() or 1)
+        self.macs = ring_macs(self.n, self.d, self.cs, masking=not use_ot) + (0 if not use_ot else self.n * self.cross_pairs())
+        self.threads = (self.p + 1 if not use_ot else self.p * self.p) if kind == "reference" else (os.cpu_count() or 1)
+
+    def cross_pairs(self):
+        from linreg_mpc_b200.phase1 import Schedule
+        return Schedule(self.d, self.cs).num_cross
 
     def run(self):
         """returns (seconds of phase-1 work, shares)"""
         wl = self.wl
         if self.kind == "reference":
-            shares, stats, _ = self.ref.run(self.path, self.d, self.p, wl["precision"], wl["precision_p2"], False)
+            shares, stats, _ = self.ref.run(self.path, self.d, self.p, wl["precision"], wl["precision_p2"], self.use_ot)
             wall = float(np.max(stats[:, 0]))
             # every party's run_party starts with the text parse (src/linear.c:27-102), which is
             # outside the path: subtract one (concurrent) parse
             return max(wall - self.parse_s, 1e-9), shares
         t0 = time.perf_counter()
         shares = self.orc.run(self.X, self.y, self.cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"],
-                              False, threads=self.threads)
+                              self.use_ot, threads=self.threads)
         return time.perf_counter() - t0, shares
 
     def describe(self):
-        return ("n=%d d=%d providers=%d TI masking, 64-bit: %d of the workload's pairs' worth (%.3g ring MACs); "
-                "%s; text parse (%.2f s) excluded" %
-                (self.n, self.d, self.p, len(self.cs) and self.d * (self.d + 1) // 2 + self.d, self.macs,
-                 "reference phase1.c compiled unmodified + loopback shims, one thread per party"
+        return ("n=%d d=%d providers=%d %s, %d-bit: all %d pairs of that instance, %d of them cross pairs (%.3g ring MACs); "
+                "%s; text parse (%.2f s) excluded; the shims' protobuf pack/unpack and loop-back copies are included" %
+                (self.n, self.d, self.p, "--use_ot" if self.use_ot else "TI masking", self.wl["bits_p1"],
+                 self.d * (self.d + 1) // 2 + self.d, self.cross_pairs(), self.macs,
+                 "reference phase1.c compiled unmodified + loopback shims, one thread per party (p*p threads with --use_ot)"
                  if self.kind == "reference" else "oracle port, %d threads" % self.threads, self.parse_s))
 
     def close(self):
@@ -172,15 +222,19 @@ def run_reference_arm(args, wl, cfg):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    use_ot = args.aggregation == "ot"
     total = max(1, args.steps + args.warmup)
-    budget = 150.0 / total                      # seconds per step
-    # ~0.2 s per cross pair at n = 1M (measured with this shim build); d=5 -> 14, 10 -> 48, 20 -> 176 cross pairs
-    d_s = 5
+    budget = 240.0 / total                      # seconds per step
+    # ~0.2 s per cross pair at n = 1M (measured with this shim build; ~8 s with --use_ot); d=5 -> 14, 10 -> 48, 20 -> 176 cross pairs
+    per_pair = (8.0 if use_ot else 0.2) * (min(wl["n"], 1_000_000) / 1e6)
+    d_s, n_s = 5, None
     for cand, pairs in ((20, 176), (10, 48)):
-        if 0.2 * pairs * (min(wl["n"], 1_000_000) / 1e6) <= budget:
+        if per_pair * pairs <= budget:
             d_s = cand
             break
-    smp = ReferenceSample(wl, d_s)
+    if use_ot and per_pair * 14 > budget:
+        n_s = max(4096, int(min(wl["n"], 1_000_000) * budget / (per_pair * 14)) // 256 * 256)
+    smp = ReferenceSample(wl, d_s, n_sample=n_s, use_ot=use_ot)
     for _ in range(args.warmup):
         smp.run()
     secs = [smp.run()[0] for _ in range(args.steps)]
@@ -189,7 +243,8 @@ def run_reference_arm(args, wl, cfg):
     value = smp.macs / t / 1e9
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int64", "data": "synthetic", "config": cfg,
+            "vs_baseline": None, "dtype": "int64" if wl["bits_p1"] == 64 else "int32", "data": "synthetic", "config": cfg,
+            "step_is": "one pass of the reference over the bounded sample described in cpu_baseline.sample (a rate, not the full workload)",
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": smp.threads, "kind": smp.kind, "sample": smp.describe()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "host_cores": os.cpu_count()}
@@ -206,18 +261,26 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
-    ap.add_argument("--aggregation", default="masking", choices=["masking", "masking-seeded"])
+    ap.add_argument("--aggregation", default="masking", choices=["masking", "masking-split", "masking-seeded", "ot"],
+                    help="masking: fused masking loop (one kernel per batch); masking-split: TI / party kernels one by one; "
+                         "masking-seeded: providers expand their own masks; ot: --use_ot correlated-OT aggregation on a sample of the cross pairs")
+    ap.add_argument("--ot-pairs", type=int, default=1000, help="cross pairs (inner products) of the --use_ot schedule per step")
     ap.add_argument("--gram", default="auto", choices=["auto", "imad", "tcgen05"])
     ap.add_argument("--batch-pairs", type=int, default=0)
     ap.add_argument("--pipes", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (p1_ctx_set_option), repeatable")
     ap.add_argument("--wire-sample", type=int, default=3300, help="cross pairs to time with GPU (de)serialisation of every message (0 = skip)")
-    ap.add_argument("--ot-sample", type=int, default=2, help="inner products of the --use_ot path to time (0 = skip)")
+    ap.add_argument("--ot-sample", type=int, default=8, help="masking workloads: inner products of the --use_ot path to time as a side figure (0 = skip)")
+    ap.add_argument("--min-sampled-s", type=float, default=2.0, help="short steps are repeated for at least this long under the clock sampler")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
-    agg = "TI masking protocol" + (" (CSP-seeded masks)" if args.aggregation == "masking-seeded" else "")
+    use_ot = args.aggregation == "ot"
+    agg = {"masking": "TI masking protocol", "masking-split": "TI masking protocol (split kernels)",
+           "masking-seeded": "TI masking protocol (CSP-seeded masks)",
+           "ot": "--use_ot correlated-OT aggregation, first %d cross pairs of the schedule" % args.ot_pairs}[args.aggregation]
     cfg = workload_config(args.workload, wl, agg)
     if args.impl == "reference":
         return run_reference_arm(args, wl, cfg)
@@ -243,13 +306,12 @@ def main():
         group = dist.group.WORLD
 
     import linreg_mpc_b200 as pkg
-    from linreg_mpc_b200.phase1 import Phase1Box
+    from linreg_mpc_b200.phase1 import Phase1Box, shard_rows
     lib = pkg.P1Lib()
     n, d, p = wl["n"], wl["d"], wl["p"]
     cs = even_col_start(d, p)
     w = wl["bits_p1"] // 8
     # row shards: boundaries on multiples of 256 rows (16-byte aligned mask slices, whole OT tiles)
-    from linreg_mpc_b200.phase1 import shard_rows
     row0, n_rows = shard_rows(n, world, rank)
     per = shard_rows(n, world, 0)[1]
     assert n_rows > 0, "more ranks than 256-row blocks"
@@ -270,7 +332,7 @@ def main():
     torch.cuda.synchronize()
 
     gram = {"auto": pkg.ffi.P1_GRAM_AUTO, "imad": pkg.ffi.P1_GRAM_IMAD, "tcgen05": pkg.ffi.P1_GRAM_TCGEN05}[args.gram]
-    batch = args.batch_pairs or max(1, min(256, (256 << 20) // max(1, n_rows * w)))   # ~256 MB of masks per vector buffer
+    batch = args.batch_pairs or max(1, min(256, (256 << 20) // max(1, n_rows * w)))   # ~256 MB per message buffer
     box = Phase1Box(lib, n, d, cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
                     row0=row0, n_rows=n_rows, batch_pairs=batch, pipes=args.pipes, gram_algo=gram, group=group)
     for o in args.opt:
@@ -278,8 +340,15 @@ def main():
         for c in box.ctxs:
             lib.check(lib.p1_ctx_set_option(c, name.encode(), int(val)))
     key = bytes(range(16))
+    ot_key = bytes(range(16, 32))
     seeded = args.aggregation == "masking-seeded"
-    macs = box.sched.ring_macs(n, masking=True)
+    fused = args.aggregation == "masking"
+    C_all = box.sched.num_cross
+    C = min(C_all, args.ot_pairs) if use_ot else C_all     # cross pairs one step executes
+    L_pairs = int(np.count_nonzero(box.sched.kind == 1))
+    # ring MACs of the reference's schedule: n (L + 3C) with masking; with --use_ot a cross pair is
+    # one Gilboa product = n ring multiplications
+    macs = n * (L_pairs + (C if use_ot else 3 * C))
     macs_gram_p1 = n * (d * (d + 1) // 2)   # the p = 1 full-Gram figure
 
     def barrier():
@@ -289,7 +358,14 @@ def main():
             torch.cuda.synchronize()
 
     def step(X, y):
-        return box.run_masking(X, y, key, seeded=seeded)
+        if not use_ot:
+            return box.run_masking(X, y, key, seeded=seeded, fused=fused)
+        box.reset()
+        box.encode(X, y)
+        box.local_blocks()
+        box.cross_pairs_ot(ot_key, max_pairs=C)
+        box.all_reduce()
+        return box.finalize()
 
     s0 = torch.cuda.ExternalStream(int(lib.p1_ctx_stream(box.ctxs[0])), device=dev)
 
@@ -308,9 +384,23 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms[0]) / k, float(ms[1]) / k
 
+    # ---- measured dense int8 tensor peak of this GPU (no int8 entry in MEASURED_PEAKS.json): tcgen05 kind::i8 probe
+    int8 = None
+    if rank == 0:
+        int8 = {}
+        for ncols in (256, 192):
+            tops, ms = ctypes.c_double(), ctypes.c_double()
+            smp = ClockSampler(local)
+            lib.check(lib.p1_probe_tensor_i8(box.ctxs[0], ncols, 400.0, ctypes.byref(tops), ctypes.byref(ms), None))
+            ck = smp.stop()
+            int8["n%d" % ncols] = {"tops": tops.value, "ms": ms.value, "sm_mhz": ck["sm_mhz"], "reasons": ck["reasons"], "samples": ck["samples"]}
+        int8["how"] = ("p1_probe_tensor_i8: one CTA per SM, back-to-back tcgen05.mma cta_group::1 kind::i8 M=128 N=256|192 K=32 on "
+                       "smem-resident operands for >= 400 ms (k_probe.cu); n192 is the Gram kernel's instruction shape for 3-digit words")
+    barrier()
+
     # ---- warm-up, then the timed region (device-resident inputs)
     shares = None
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(args.warmup, 3)):
         shares = step(Xd, yd)
     for c in box.ctxs:
         lib.check(lib.p1_ctx_profile(c, 1))
@@ -333,6 +423,19 @@ def main():
     for c in box.ctxs:
         lib.check(lib.p1_ctx_profile(c, 0))
 
+    # ---- short steps: the same step repeated for >= min_sampled_s under the sampler, so that the clock record
+    # has enough samples (a 3 ms step x 5 is shorter than any sampling period) and the rate is a sustained one
+    sustained = None
+    if ms_wall * args.steps < args.min_sampled_s * 1e3:
+        reps = int(math.ceil(args.min_sampled_s * 1e3 / max(ms_wall, 1e-3)))
+        smp2 = ClockSampler(local) if rank == 0 else None
+        ms_sus, _ = timed(lambda: step(Xd, yd), reps)
+        ck2 = smp2.stop() if smp2 else None
+        sustained = {"steps": reps, "ms_per_step": ms_sus, "value": macs / (ms_sus * 1e-3) / 1e9, "clocks": ck2}
+        if clocks is not None and ck2 is not None and clocks["samples"] < 10:
+            clocks = dict(ck2, note="sampled over the %d back-to-back repetitions of the step that follow the timed region "
+                                    "(the %d timed steps last %.1f ms in total)" % (reps, args.steps, ms_wall * args.steps))
+
     # ---- roofline of the dominant kernel (algorithmic bytes / flops per launch)
     peaks = {}
     try:
@@ -342,11 +445,16 @@ def main():
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
-    # no int8 entry in MEASURED_PEAKS.json: dense int8 = 2x dense bf16 on this part, so 2x the measured bf16 burst
-    int8_peak = 2.0 * float(peaks.get("bf16_tflops", 1590.0))
+    if group is not None:   # rank 0 measured the int8 peak
+        t8 = torch.tensor([int8["n256"]["tops"] if int8 else 0.0], dtype=torch.float64, device=dev)
+        dist.broadcast(t8, src=0)
+        int8_peak = float(t8[0])
+    else:
+        int8_peak = int8["n256"]["tops"]
     int8_nominal = 4500.0
-    C = box.sched.num_cross
     nb = n_rows * w
+    sm_clk = (clocks or {}).get("sm_mhz") or 1965.0
+    lsu_lanes = 148 * 32 * sm_clk * 1e6            # shared-memory lookups per second at one 32-lane LDS per clock per SM
     local_macs, tc_ops, limb_bytes = 0, 0, 0
     for k in range(box.sched.num_dp):
         lo, hi = box.sched.col_range(k)
@@ -357,37 +465,46 @@ def main():
         local_macs += n_rows * pairs
         tc_ops += 2 * Lk.value ** 2 * n_rows * pairs         # int8 ops of the lower-triangle pairs (executed digits)
         limb_bytes += m * n_rows * (w + Lk.value)
+    cots = C * n_rows * wl["bits_p1"] if use_ot else 0
     alg_bytes = {  # per step on this rank
         "encode": (8 + w) * (n_rows * d + n_rows),
         "ti_generate": C * (2 * nb) * (1 if not seeded else 2),     # keystream words written
         "party_b_mask": C * 3 * nb,                                  # column + mask read, message written
         "party_a_step": C * 4 * nb,                                  # column, mask, peer message read; message written
         "party_b_share": C * 2 * nb,                                 # peer message + column read
+        "masking_fused": C * 4 * nb,                                 # columns a_i, b_j read; messages b->a, a->b written
         "gram_imad": (d + 1) * nb,                                   # every owned column read once
         "gram_limbs": limb_bytes,                                    # words read, digit planes written
+        "cot_recv": cots * (16 + w),                                 # U written (16 B / OT), pads stashed
+        "cot_send": cots * (16 + w),                                 # U read, C written
+        "cot_finish": cots * 2 * w,                                  # pads + C read
     }
+    # shared-memory lookups per unit for the kernels whose limiter is the LDS port (T-table AES):
+    # TI / fused loop: 135 per 16-byte keystream block; OT tile kernels per OT: receiver 2 PRG blocks
+    # (4 + 144 lookups each with the column key in registers) + 1 hash (160), sender 1 PRG + 2 hashes
+    lds_per_unit = {"ti_generate": 135.0, "masking_fused": 135.0, "cot_recv": 2 * 148 + 160.0, "cot_send": 148 + 320.0}
+    units = {"ti_generate": C * (2 * nb + 16) / 16.0 * (1 if not seeded else 2), "masking_fused": C * (2 * nb + 16) / 16.0,
+             "cot_recv": float(cots), "cot_send": float(cots)}
     kernels = {}
     for name, pr in prof.items():
         ent = dict(pr)
+        sec = pr["ms_per_step"] * 1e-3
         if alg_bytes.get(name):
-            gbs = alg_bytes[name] / (pr["ms_per_step"] * 1e-3) / 1e9
+            gbs = alg_bytes[name] / sec / 1e9
             ent.update(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak)
         if name == "gram_tc" and tc_ops:
-            tops = tc_ops / (pr["ms_per_step"] * 1e-3) / 1e12
+            tops = tc_ops / sec / 1e12
             ent.update(bound="tensor", achieved=tops, peak=int8_peak, unit="TOP/s (int8)", frac=tops / int8_peak,
-                       frac_of_nominal_dense_int8=tops / int8_nominal, ring_gmacs=local_macs / (pr["ms_per_step"] * 1e-3) / 1e9,
-                       peak_source="2 x measured dense bf16 burst (no int8 entry in MEASURED_PEAKS.json); nominal dense int8 is 4500")
-        if name == "ti_generate":
-            # the honest bound of the T-table AES: 16 lookups x 10 rounds, minus the 12 + 15 of rounds 1-2 that the
-            # CTR structure removes, plus 15 per 8 blocks for the group cache = 135 shared-memory lookups per
-            # 16-byte block; one 32-lane LDS per clock per SM
-            blocks = C * (2 * nb + 16) / 16.0 * (1 if not seeded else 2)
-            sm_clk = (clocks or {}).get("sm_mhz") or 1965.0
-            lsu_peak = 148 * 32 * sm_clk * 1e6 / 135.0          # blocks/s at one LDS per clock per SM
-            ent.update(lsu_bound={"achieved_blocks_per_s": blocks / (pr["ms_per_step"] * 1e-3), "peak_blocks_per_s": lsu_peak,
-                                  "frac": blocks / (pr["ms_per_step"] * 1e-3) / lsu_peak,
-                                  "note": "135 LDS per AES block, 128 B/clk/SM shared-memory port, at the sampled SM clock; "
-                                          "the kernel's own time includes waiting behind the other pipe's co-resident party kernels"})
+                       frac_of_nominal_dense_int8=tops / int8_nominal, ring_gmacs=local_macs / sec / 1e9,
+                       peak_source="measured in this run by p1_probe_tensor_i8 (tcgen05 kind::i8, M=128 N=256 K=32, operands resident in "
+                                   "shared memory); nominal dense int8 is 4500")
+        if name in lds_per_unit and units.get(name):
+            rate = units[name] / sec
+            peak = lsu_lanes / lds_per_unit[name]
+            ent.update(lsu_bound={"achieved_per_s": rate, "peak_per_s": peak, "frac": rate / peak,
+                                  "unit": "AES blocks" if name in ("ti_generate", "masking_fused") else "correlated OTs",
+                                  "lookups_per_unit": lds_per_unit[name],
+                                  "note": "shared-memory port: one 32-lane LDS per clock per SM at the sampled SM clock (%.0f MHz)" % sm_clk})
         kernels[name] = ent
     dominant = max(prof, key=lambda k: prof[k]["ms_per_step"]) if prof else None
     roofline = None
@@ -400,10 +517,12 @@ def main():
             roofline["algorithmic_bytes_per_launch"] = alg_bytes[dominant] / max(kd["launches_per_step"], 1)
         if "lsu_bound" in kd:
             roofline["lsu_bound"] = kd["lsu_bound"]
+            roofline["note"] = ("this kernel is bound by shared-memory lookups (T-table AES), not by HBM: lsu_bound is its roofline; "
+                                "the hbm figures are the required keys")
         try:   # DRAM bytes per launch of this kernel from the committed ncu --set full capture, if the shape matches
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 tr = json.load(f).get(dominant)
-            if tr and (dominant != "ti_generate" or (tr["pairs"] == batch and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"])):
+            if tr and (tr.get("pairs") is None or (tr["pairs"] == batch and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"])):
                 roofline["traffic"] = tr["bytes_per_launch"]
                 roofline["traffic_source"] = tr["source"]
         except (OSError, ValueError, KeyError):
@@ -424,89 +543,103 @@ def main():
         d2h = world * (p * box.acc_len * 8)
         e2e = {"value": macs / (ms_e2e * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+        del Xh, yh
+
+    # ---- parity of the timed configuration (outside the timed region, every N; collective)
+    check = None
+    if not args.no_check:
+        from oracle import pyoracle as po
+        from tools.parity_check import check_run
+        shares = step(Xd, yd)
+        only = None
+        if use_ot:      # the sample covers the first C inner products of the schedule: those slots, plus every local pair
+            done, only = 0, []
+            for ps, pr, items in box.ot_schedule():
+                for (_, _, slot) in items:
+                    if done < C:
+                        only.append(slot)
+                        done += 1
+            L1 = box.sched.kind == 1
+            only = np.unique(np.concatenate([np.array(only, dtype=np.int64), box.sched.slot[L1]]))
+        check = check_run(lib, po.Oracle(), box, shares, Xd, yd, samples=16, diag_samples=4, only_slots=only)
+        check["shares_nonzero"] = bool(np.any(shares))
+        check["what"] = ("sum over providers of every pre-shift share word == one-provider tcgen05 Gram (all off-diagonal + share_b words), "
+                         "all diagonal words and statistics, sampled words vs the CPU oracle's ring dot / sequential double diagonal")
 
     # ---- the same protocol with every message through the protobuf wire format on the GPU (what separate
     # boxes execute per pair, minus the network): a bounded sample of the cross pairs, extrapolated
     wire = None
-    if args.wire_sample > 0 and C:
-        npairs = min(C, args.wire_sample)
+    if args.wire_sample > 0 and C_all and not use_ot:
+        npairs = min(C_all, args.wire_sample)
 
-        def wire_step(w):
-            box.cross_pairs_masking(key, seeded=seeded, wire=w, max_pairs=npairs)
+        def wire_step(wv):
+            box.cross_pairs_masking(key, seeded=seeded, wire=wv, max_pairs=npairs, fused=(fused and not wv))
             box.sync()
         wire_step(True)
         ms_w, _ = timed(lambda: wire_step(True), 1)
         ms_p, _ = timed(lambda: wire_step(False), 1)
+        ms_all_wire = ms_step + (ms_w - ms_p) / npairs * C_all
         wire = {"pairs": npairs, "ms_with_wire": ms_w, "ms_plain": ms_p, "us_per_pair_with_wire": ms_w * 1e3 / npairs,
-                "us_per_pair_plain": ms_p * 1e3 / npairs, "all_cross_pairs_ms_extrapolated": ms_w / npairs * C,
-                "messages_per_pair": 4, "note": "p1_msg_pack + p1_msg_unpack around each of the 4 messages of a pair "
-                "(src/phase1.c:100-145); the headline step hands messages over on the device"}
+                "us_per_pair_plain": ms_p * 1e3 / npairs, "all_cross_pairs_ms_extrapolated": ms_w / npairs * C_all,
+                "step_ms_with_wire_extrapolated": ms_all_wire, "value_with_wire": macs / (ms_all_wire * 1e-3) / 1e9,
+                "messages_per_pair": 4, "note": "split TI / party kernels with p1_msg_pack + p1_msg_unpack around each of the 4 messages of a pair "
+                "(src/phase1.c:100-145): what parties on separate boxes execute, minus the network; the headline step keeps all "
+                "parties on one device and hands messages over in HBM"}
 
-    # ---- --use_ot aggregation (BASELINE config 3 names it): a bounded sample of inner products over this
-    # rank's rows through the correlated-OT kernels, reported as COT/s with the extrapolation to all cross pairs
+    # ---- --use_ot as a side figure of the masking workloads (the OT workload itself: --aggregation ot)
     ot = None
-    if args.ot_sample > 0 and C:
-        from linreg_mpc_b200.phase1 import derive_cot_session, _bits128
-        L_, ctx0 = lib, box.ctxs[0]
-        s0_, s1_, delta_ = derive_cot_session(bytes(range(16, 32)), 3, 4)
-        chosen_ = np.where(_bits128(delta_)[:, None], s1_, s0_)
-        snd, rcv = ctypes.c_void_p(), ctypes.c_void_p()
-        L_.check(L_.p1_cot_sender_new(ctx0, delta_.tobytes(), pkg.ffi.ptr(np.ascontiguousarray(chosen_)), ctypes.byref(snd)))
-        L_.check(L_.p1_cot_receiver_new(ctx0, pkg.ffi.ptr(s0_), pkg.ffi.ptr(s1_), ctypes.byref(rcv)))
-        ub = torch.empty(int(L_.p1_cot_u_bytes(ctx0, n_rows)), dtype=torch.uint8, device=dev)
-        cb = torch.empty(int(L_.p1_cot_c_bytes(ctx0, n_rows)), dtype=torch.uint8, device=dev)
-        acc_ot = torch.zeros(box.acc_len, dtype=torch.int64, device=dev)
-        torch.cuda.synchronize()
-
+    if args.ot_sample > 0 and C_all and not use_ot:
         def ot_step():
-            for t in range(args.ot_sample):
-                L_.check(L_.p1_cot_receiver_extend(ctx0, rcv, box.data, d - 1, n, row0, pkg.ffi.ptr(ub)))
-                L_.check(L_.p1_cot_sender_step(ctx0, snd, box.data, t % (d // p), n, row0, pkg.ffi.ptr(ub), pkg.ffi.ptr(cb),
-                                               pkg.ffi.ptr(acc_ot), t))
-                L_.check(L_.p1_cot_receiver_finish(ctx0, rcv, pkg.ffi.ptr(cb), pkg.ffi.ptr(acc_ot), t))
+            box.cross_pairs_ot(ot_key, max_pairs=args.ot_sample)
         ot_step()
         ms_ot, _ = timed(ot_step, 2)
-        cots = args.ot_sample * n * wl["bits_p1"]
-        rate = cots / (ms_ot * 1e-3)
-        total_cots = C * n * wl["bits_p1"]
-        ot = {"inner_products": args.ot_sample, "cots": cots, "ms": ms_ot, "cot_per_s": rate,
+        c_s = args.ot_sample * n * wl["bits_p1"]
+        rate = c_s / (ms_ot * 1e-3)
+        total_cots = C_all * n * wl["bits_p1"]
+        ot = {"inner_products": args.ot_sample, "cots": c_s, "ms": ms_ot, "cot_per_s": rate,
               "wire_bytes_per_cot": 16 + w, "all_cross_pairs_cots": total_cots, "all_cross_pairs_seconds_extrapolated": total_cots / rate,
-              "note": "reference protocol needs n*W correlated OTs per cross pair (src/phase1.c:58-65); reported, not the headline"}
-        L_.p1_cot_free(snd)
-        L_.p1_cot_free(rcv)
-
-    # ---- parity property at full size: the providers' shares sum to the plain ring Gram of the encoded data
-    check = None
-    if rank == 0 and shares is not None:
-        check = {"shares_nonzero": bool(np.any(shares))}
+              "note": "session setup included; see --aggregation ot for the workload, its kernel table and its scaling"}
 
     # ---- CPU baseline (rank 0, N = 1 only): the reference's own phase-1 code on a bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        smp = ReferenceSample(wl, 10)
+        smp = ReferenceSample(wl, 5 if use_ot else 20, n_sample=min(n, 131072) if use_ot else None, use_ot=use_ot)
         secs, ref_shares = smp.run()
         cpu = {"value": smp.macs / secs / 1e9, "unit": UNIT, "cores": smp.threads, "kind": smp.kind,
                "sample": smp.describe(), "seconds": secs, "host_cores": os.cpu_count()}
         # the same sample through the GPU path: every share word must match the reference's
         sbox = Phase1Box(lib, smp.n, smp.d, smp.cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"],
                          device=local, batch_pairs=8)
-        got = sbox.run_masking(smp.X, smp.y, key)
+        got = sbox.run_ot(smp.X, smp.y, ot_key) if use_ot else sbox.run_masking(smp.X, smp.y, key)
         sbox.close()
         cpu["gpu_shares_match_sample"] = bool(np.array_equal(got, ref_shares))
         smp.close()
 
     box.close()
     if rank == 0:
-        line = {"metric": METRIC, "value": macs / (ms_step * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 1), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        value = macs / (ms_step * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "int64" if w == 8 else "int32", "data": "synthetic",
-                "config": dict(cfg, rows_per_rank=per, batch_pairs=batch, gram=args.gram,
+                "config": dict(cfg, rows_per_rank=per, batch_pairs=batch, gram=args.gram, pipes=args.pipes,
+                               cross_pairs_per_step=C, cross_pairs_of_workload=C_all,
                                l2="inputs (%.1f GB of columns + %.1f GB of messages per step) exceed the 126 MB L2"
-                                  % ((d + 1) * nb / 1e9, C * 4 * nb / 1e9)),
+                                  % ((d + 1) * nb / 1e9, C * (2 if not use_ot else 3 * 8) * nb / 1e9)),
                 "ring_macs_per_step": macs, "share_time_ms": ms_step, "wall_ms_per_step": ms_wall,
                 "gram_p1_equiv_macs": macs_gram_p1,
                 "gpu_launches": int(launches) * world, "kernels": kernels, "roofline": roofline, "clocks": clocks,
+                "sustained": sustained, "int8_peak_probe": int8,
                 "e2e": e2e, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
+        if wire:
+            line["value_with_wire"] = wire["value_with_wire"]
+        if use_ot:
+            cot_total = C * n * wl["bits_p1"]
+            line["use_ot"] = {"cot_per_s": cot_total / (ms_step * 1e-3), "cots_per_step": cot_total, "inner_products_per_step": C,
+                              "wire_bytes_per_cot": 16 + w,
+                              "workload_cots": C_all * n * wl["bits_p1"],
+                              "workload_seconds_extrapolated": ms_step * 1e-3 / max(C, 1) * C_all,
+                              "note": "the step includes encode, the local blocks and the finalize tail; the extrapolation to all %d "
+                                      "cross pairs of the workload is linear in the pair count" % C_all}
         print(json.dumps(line))
     if group is not None:
         dist.destroy_process_group()
