@@ -104,6 +104,14 @@ int p1_host_alloc(p1_ctx *ctx, size_t bytes, void **host);
 int p1_host_free(p1_ctx *ctx, void *host);
 int p1_copy_h2d(p1_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
 int p1_copy_d2h(p1_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes); /* synchronises */
+/* device -> host without waiting (dst_host page-locked for a truly asynchronous copy); the data is there after
+ * p1_ctx_sync, or after p1_ctx_mark_sync on a mark recorded behind the copy */
+int p1_copy_d2h_async(p1_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes);
+/* markers on the context's stream (slot 0..7): p1_ctx_mark records one behind everything enqueued so far,
+ * p1_ctx_mark_sync blocks the calling host thread until the work before the mark is done - while later work
+ * (the next batch) keeps running.  This is what lets the host file send batch k while the GPU prepares k+1. */
+int p1_ctx_mark(p1_ctx *ctx, int slot);
+int p1_ctx_mark_sync(p1_ctx *ctx, int slot);
 
 /* ------------------------------------------------------------------ a2-a4: encode
  * Replaces the arithmetic of read_matrix / read_vector (src/linear.c:46-51,83-87):
@@ -362,6 +370,86 @@ int p1_share_bits(p1_ctx *ctx, const void *shares, size_t n, uint8_t *sel);
  * l values of y.  Synchronises the stream. */
 int p1_parse_doubles(p1_ctx *ctx, const char *text, size_t bytes, double *out_dev, size_t max_tokens,
                      uint64_t *n_tokens, uint64_t *n_deferred, uint64_t *deferred, size_t cap);
+
+/* ------------------------------------------------------------------ 8b/8e: row sharding behind the boundary
+ * A p1_group owns one context per GPU of the box inside ONE process, so that the reference's callers
+ * (run_party / run_trusted_initializer, src/phase1.h:14-29, one process per party) use every GPU.
+ * Rows of the provider's X, y are split into equal 256-row aligned slabs (device g holds rows
+ * [row0_g, row0_g + rows_g), p1_group_rows); every call below fans out over the devices on their rows
+ * and is asynchronous like its single-device counterpart, ordered with plain calls on
+ * p1_group_ctx(grp, 0) (device 0's stream is the group's main stream).  Partial shares combine exactly
+ * by the wrapping u64 sum p1_group_reduce performs (peers' accumulators read over NVLink by one kernel
+ * on device 0; option "reduce" = 1: ncclAllReduce(ncclUint64, ncclSum) from the system libnccl.so.2).
+ * The devices must have peer access to each other.  Listing one device twice is allowed (tests).
+ * A group and everything made from it belong to one host thread at a time; the per-peer threads of OT
+ * mode (src/phase1.c:503-513) each create their own group and may share one p1_gdata (read only). */
+typedef struct p1_group p1_group;
+typedef struct p1_gdata p1_gdata;     /* encoded X, y as one p1_data per device */
+typedef struct p1_gvec p1_gvec;       /* a batch of n-row vectors as row slices on the devices */
+typedef struct p1_gcot p1_gcot;       /* one correlated-OT session, one p1_cot per device */
+
+int p1_group_create(const int *devices, int ndev, int ring_bits_p1, int ring_bits_p2, p1_group **grp);
+void p1_group_destroy(p1_group *grp);
+int p1_group_size(const p1_group *grp);
+p1_ctx *p1_group_ctx(p1_group *grp, int g);
+void p1_group_rows(const p1_group *grp, size_t n_total, int g, size_t *row0, size_t *n_rows);
+/* "reduce" (see above); every other name is forwarded to p1_ctx_set_option of each context */
+int p1_group_set_option(p1_group *grp, const char *name, long value);
+int p1_group_sync(p1_group *grp);
+uint64_t p1_group_launches(p1_group *grp);
+
+/* p1_encode over the group: X (n x d row-major doubles) and y on the host - every device pulls its slab
+ * over its own PCIe link - or on a device of the group (the other devices read it over NVLink). */
+int p1_group_encode(p1_group *grp, const double *X, const double *y, size_t n, size_t d,
+                    double normalizer, int precision, p1_gdata **out);
+void p1_gdata_free(p1_gdata *data);
+const p1_data *p1_gdata_shard(const p1_gdata *data, int g);
+
+/* the group's accumulators: p1_acc_len(d) words per device, zeroed by p1_group_acc_reset; every call
+ * below adds into them; p1_group_reduce leaves their sum in device 0's (p1_group_acc_dev(grp, 0)) */
+int p1_group_acc_reset(p1_group *grp, size_t d);
+uint64_t *p1_group_acc_dev(p1_group *grp, int g);
+int p1_group_reduce(p1_group *grp);
+
+/* p1_local_block on every slab (src/phase1.c:562-571) */
+int p1_group_local_block(p1_group *grp, const p1_gdata *data, size_t col_lo, size_t col_hi, int owns_target, int algo);
+
+/* batch x n_total ring words as row slices; gather / scatter move whole vectors (ld0 words apart) on
+ * device 0 - where p1_msg_pack / p1_msg_unpack work - from / to the slices with peer copies */
+int p1_gvec_alloc(p1_group *grp, size_t n_total, size_t batch, p1_gvec **out);
+void p1_gvec_free(p1_gvec *v);
+void *p1_gvec_dev(const p1_gvec *v, int g, size_t *ld_words);
+int p1_gvec_gather(p1_group *grp, const p1_gvec *v, size_t count, void *full_dev0, size_t ld0);
+int p1_gvec_scatter(p1_group *grp, const void *full_dev0, size_t ld0, size_t count, p1_gvec *v);
+
+/* p1_ti_generate / p1_party_* / p1_acc_sub_values over the group; xy (sum over ALL rows), r and the
+ * values live on device 0; cols / slots: host or device-0... host arrays (each context stages its copy) */
+int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total,
+                         p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0);
+int p1_group_party_b_mask(p1_group *grp, const p1_gdata *data, const int32_t *cols, size_t count, const p1_gvec *T, p1_gvec *out);
+int p1_group_party_a_step(p1_group *grp, const p1_gdata *data, const int32_t *cols, const int64_t *slots, size_t count,
+                          const p1_gvec *T, const p1_gvec *in, p1_gvec *out);
+int p1_group_party_b_share(p1_group *grp, const p1_gdata *data, const int32_t *cols, const int64_t *slots, size_t count, const p1_gvec *in);
+int p1_group_acc_sub_values(p1_group *grp, size_t d, const int64_t *slots, const uint64_t *value_dev0, size_t count);
+
+/* --use_ot over the group: every device extends / answers the OTs of its rows and moves its slice of
+ * the wire messages U (p1_cot_u_bytes(n) bytes) and C (p1_cot_c_bytes(n)) from / to the HOST buffers over
+ * its own PCIe link (page-locked buffers from p1_host_alloc make the copies concurrent).  The calls
+ * return when the host buffer they produce is complete. */
+int p1_group_cot_sender_new(p1_group *grp, const uint8_t delta[16], const uint8_t seeds[128][16], p1_gcot **s);
+int p1_group_cot_receiver_new(p1_group *grp, const uint8_t seeds0[128][16], const uint8_t seeds1[128][16], p1_gcot **r);
+void p1_group_cot_free(p1_gcot *session);
+int p1_group_cot_receiver_extend(p1_group *grp, p1_gcot *r, const p1_gdata *data, int32_t col, void *u_host);
+int p1_group_cot_sender_step(p1_group *grp, p1_gcot *s, const p1_gdata *data, int32_t col, const void *u_host, void *c_host, int64_t slot);
+int p1_group_cot_receiver_finish(p1_group *grp, p1_gcot *r, const p1_gdata *data, const void *c_host, int64_t slot);
+
+/* p1_finalize for the group (src/phase1.c:605-641): p1_group_reduce, the diagonal of the owned columns
+ * [col_lo, col_hi) (exact shortcut, or the sequential double loop chained over the slabs in device
+ * order), the 64 -> 32 shift, calloc'ed outputs the caller free()s.  acc_host: NULL = the group's own
+ * accumulators; else p1_acc_len(d) words on the host that are already the sum over devices and threads (the
+ * per-peer threads of OT mode keep private results that the caller adds up, src/phase1.c:514-523). */
+int p1_group_finalize(p1_group *grp, const p1_gdata *data, const uint64_t *acc_host, size_t col_lo, size_t col_hi,
+                      int precision, int precision_p2, double normalizer2, void **res_A, void **res_b);
 
 #ifdef __cplusplus
 }

@@ -92,74 +92,124 @@ __device__ __forceinline__ uint32_t cot_transpose32(uint32_t x, uint32_t lane) {
 	return x;
 }
 
-// ROLE 0: receiver extend, ROLE 1: sender step
+// ROLE 0: receiver extend, ROLE 1: sender step.  TPI = tiles a 128-thread group works on per iteration
+// (independent AES chains per thread: 2 for both roles - the receiver's two PRG blocks of one tile, the
+// sender's PRG blocks of two tiles; then 1 / 4 independent hashes).
+// Shared memory: [transpose rows: COT_GROUPS x TPI x 2 buffers x 128 x 5 words | gap | AES tables].  The rows
+// are double buffered, so one named barrier per iteration suffices: a group writes buffer i&1 in
+// iteration i while stragglers may still read buffer (i-1)&1.
 template <typename W, int ROLE>
 __global__ void __launch_bounds__(COT_THREADS, 1) k_cot_tiles(const CotParams P) {
 	extern __shared__ __align__(256) uint8_t smem[];
-	constexpr int NK = ROLE == 0 ? 2 : 1;
+	constexpr int TPI = ROLE == 1 ? 2 : 1;
 	constexpr int WB = sizeof(W) * 8;
-	// [key schedules NK x 44 x 128 | gap | AES tables (64 KB aligned) | transpose rows COT_GROUPS x 128 x 5]
-	uint32_t *sK = reinterpret_cast<uint32_t *>(smem);
-	uint8_t *sT = smem + aes_table_offset(smem, NK * 44 * 128 * 4, COT_GROUPS * 128 * 5 * 4);
-	uint32_t *sR = reinterpret_cast<uint32_t *>(sT + AES_TAB_BYTES);
+	constexpr int ROWS = 128 * 5;                     // words of one transposed tile (row stride 5: conflict free)
+	uint32_t *sR = reinterpret_cast<uint32_t *>(smem);
+	uint8_t *sT = smem + aes_table_offset(smem, COT_GROUPS * TPI * 2 * ROWS * 4, 0);
 	aes_load_tables(sT, P.T0);
-	for(int i = threadIdx.x; i < NK * 44 * 128; i += blockDim.x) sK[i] = P.keys[i];
 	__syncthreads();
 	const int g = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5, lane = t & 31;
 	const uint32_t lb = aes_lane_base(sT, (uint32_t) lane);
-	uint32_t *myR = sR + g * 128 * 5;
+	uint32_t *myR = sR + g * (TPI * 2 * ROWS);
 	const bool dbit = ROLE == 1 && ((P.delta[t >> 5] >> (t & 31)) & 1);
-	const AesSmemKey k0s(sK, 128, t), k1s(sK + 44 * 128, 128, t);
+	// the column keys of thread t: expanded schedules in global memory (read once; again only when the PRG
+	// block counter crosses a multiple of 2^32)
+	const AesSmemKey k0s(P.keys, 128, t), k1s(P.keys + 44 * 128, 128, t);
 	AesRegCtrKey K0, K1;
 	aes_regkey_init(k0s, lb, (uint32_t) (P.ctr0 >> 32), K0);
 	if(ROLE == 0) aes_regkey_init(k1s, lb, (uint32_t) (P.ctr0 >> 32), K1);
 	uint64_t dot = 0;
-	for(uint64_t tile = (uint64_t) blockIdx.x * COT_GROUPS + g; tile < P.tiles; tile += (uint64_t) gridDim.x * COT_GROUPS) {
-		// ---- column phase: thread t = column t of the kappa x m matrix
-		const uint64_t blk = P.ctr0 + tile;
-		if((uint32_t) (blk >> 32) != K0.hi) {                                                       // uniform over the group
-			aes_regkey_init(k0s, lb, (uint32_t) (blk >> 32), K0);
-			if(ROLE == 0) aes_regkey_init(k1s, lb, (uint32_t) (blk >> 32), K1);
-		}
-		uint32_t a[4];
-		aes_ctr_block_r(K0, lb, (uint32_t) blk, a);
-		uint4 *up = reinterpret_cast<uint4 *>((char *) P.u + tile * 2048) + t;
-		if(ROLE == 0) {
-			uint32_t b[4];
-			aes_ctr_block_r(K1, lb, (uint32_t) blk, b);
-			const uint4 ch = *(reinterpret_cast<const uint4 *>(P.col) + tile); // 128 choice bits = 16 bytes of the column
-			*up = make_uint4(a[0] ^ b[0] ^ ch.x, a[1] ^ b[1] ^ ch.y, a[2] ^ b[2] ^ ch.z, a[3] ^ b[3] ^ ch.w);
-		} else if(dbit) {
-			const uint4 uv = *up;
-			a[0] ^= uv.x; a[1] ^= uv.y; a[2] ^= uv.z; a[3] ^= uv.w;
-		}
-		// ---- 128x128 bit transpose: four 32x32 butterflies per warp (word b of the warp's 32 columns ->
-		// word wq of rows 32b .. 32b+31), then the rows are gathered through shared memory
+	const uint64_t stride = (uint64_t) gridDim.x * COT_GROUPS * TPI;
+	uint32_t it = 0;
+	for(uint64_t tile0 = ((uint64_t) blockIdx.x * COT_GROUPS + g) * TPI; tile0 < P.tiles; tile0 += stride, it++) {
+		uint32_t *buf = myR + (it & 1) * (TPI * ROWS);
+		// ---- global operands of this iteration, requested before the AES work that hides their latency
+		uint4 uv[TPI];
+		W xk[TPI];
 #pragma unroll
-		for(int b = 0; b < 4; b++) myR[(32 * b + lane) * 5 + wq] = cot_transpose32(a[b], (uint32_t) lane);
-		group_sync(g);
-		// ---- row phase: thread t = OT t of the tile
-		uint32_t x0 = myR[t * 5 + 0], x1 = myR[t * 5 + 1], x2 = myR[t * 5 + 2], x3 = myR[t * 5 + 3];
-		group_sync(g);
-		const uint64_t J = P.J0 + tile * 128 + t;
-		x0 ^= (uint32_t) J;
-		x1 ^= (uint32_t) (J >> 32);
-		uint32_t h[4];
-		aes_encrypt(AesConstKey(P.hash), lb, x0, x1, x2, x3, h);
-		W pad0 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ x1)) << 32) | (h[0] ^ x0)) : (W) (h[0] ^ x0);
-		if(ROLE == 0) {
-			reinterpret_cast<W *>(P.pads)[tile * 128 + t] = pad0;
+		for(int z = 0; z < TPI; z++) {
+			const uint64_t tile = tile0 + z;
+			uv[z] = make_uint4(0, 0, 0, 0);
+			xk[z] = 0;
+			if(tile >= P.tiles) continue;
+			if(ROLE == 0) uv[z] = __ldg(reinterpret_cast<const uint4 *>(P.col) + tile);   // 128 choice bits = 16 bytes of the column
+			else {
+				uv[z] = __ldcs(reinterpret_cast<const uint4 *>((const char *) P.u + tile * 2048) + t);
+				const uint64_t k = (tile * 128 + t) / WB;
+				if(k < P.n_rows) xk[z] = __ldg(reinterpret_cast<const W *>(P.col) + k);
+			}
+		}
+		// ---- column phase: thread t = column t of the kappa x m matrix.  Straight-line code for all TPI tiles
+		// (a tile past the end computes on zeros and stores nothing), so the independent AES chains interleave.
+		const uint64_t blk0 = P.ctr0 + tile0;
+		const bool fast = (uint32_t) (blk0 >> 32) == K0.hi && (uint32_t) ((blk0 + TPI - 1) >> 32) == K0.hi;   // uniform over the group
+		uint32_t a[TPI][4];
+		if(fast) {
+#pragma unroll
+			for(int z = 0; z < TPI; z++) aes_ctr_block_r(K0, lb, (uint32_t) (blk0 + z), a[z]);
+			if(ROLE == 0) {
+				uint32_t b[4];
+				aes_ctr_block_r(K1, lb, (uint32_t) blk0, b);
+#pragma unroll
+				for(int c = 0; c < 4; c++) b[c] ^= a[0][c];
+				if(tile0 < P.tiles) __stcs(reinterpret_cast<uint4 *>((char *) P.u + tile0 * 2048) + t,
+					make_uint4(b[0] ^ uv[0].x, b[1] ^ uv[0].y, b[2] ^ uv[0].z, b[3] ^ uv[0].w));
+			}
 		} else {
-			uint32_t y0 = x0 ^ P.delta[0], y1 = x1 ^ P.delta[1], y2 = x2 ^ P.delta[2], y3 = x3 ^ P.delta[3];
-			aes_encrypt(AesConstKey(P.hash), lb, y0, y1, y2, y3, h);
-			W pad1 = sizeof(W) == 8 ? (W) ((((uint64_t) (h[1] ^ y1)) << 32) | (h[0] ^ y0)) : (W) (h[0] ^ y0);
-			const uint64_t ni = tile * 128 + t, k = ni / WB;
-			const int bit = (int) (ni % WB);
-			if(k < P.n_rows) {
-				W xk = reinterpret_cast<const W *>(P.col)[k];
-				W opt1 = (W) (xk << bit) + pad0; // (1 << bit) * x + opt0, src/phase1.c:50
-				reinterpret_cast<W *>(P.c)[ni] = opt1 ^ pad1;
-				dot -= (uint64_t) pad0;             // share = -sum opt0, src/phase1.c:66-68
+			// the PRG block counter crosses a multiple of 2^32 here: schedules from global memory, then re-key
+#pragma unroll
+			for(int z = 0; z < TPI; z++) aes_ctr_block_k(k0s, lb, blk0 + z, a[z]);
+			if(ROLE == 0) {
+				uint32_t b[4];
+				aes_ctr_block_k(k1s, lb, blk0, b);
+				if(tile0 < P.tiles) __stcs(reinterpret_cast<uint4 *>((char *) P.u + tile0 * 2048) + t,
+					make_uint4(a[0][0] ^ b[0] ^ uv[0].x, a[0][1] ^ b[1] ^ uv[0].y, a[0][2] ^ b[2] ^ uv[0].z, a[0][3] ^ b[3] ^ uv[0].w));
+			}
+			const uint32_t hi_next = (uint32_t) ((blk0 + stride) >> 32);
+			aes_regkey_init(k0s, lb, hi_next, K0);
+			if(ROLE == 0) aes_regkey_init(k1s, lb, hi_next, K1);
+		}
+#pragma unroll
+		for(int z = 0; z < TPI; z++) {
+			if(ROLE == 1 && dbit) { a[z][0] ^= uv[z].x; a[z][1] ^= uv[z].y; a[z][2] ^= uv[z].z; a[z][3] ^= uv[z].w; }
+			// 128x128 bit transpose: four 32x32 butterflies per warp (word b of the warp's 32 columns ->
+			// word wq of rows 32b .. 32b+31), then the rows are gathered through shared memory
+#pragma unroll
+			for(int b = 0; b < 4; b++) buf[z * ROWS + (32 * b + lane) * 5 + wq] = cot_transpose32(a[z][b], (uint32_t) lane);
+		}
+		group_sync(g);
+		// ---- row phase: thread t = OT t of each tile; all hashes first (independent chains), then the stores
+		uint32_t x[TPI][4], h0[TPI][4], h1[TPI][4];
+#pragma unroll
+		for(int z = 0; z < TPI; z++) {
+			const uint64_t J = P.J0 + (tile0 + z) * 128 + t;
+			x[z][0] = buf[z * ROWS + t * 5 + 0] ^ (uint32_t) J;
+			x[z][1] = buf[z * ROWS + t * 5 + 1] ^ (uint32_t) (J >> 32);
+			x[z][2] = buf[z * ROWS + t * 5 + 2];
+			x[z][3] = buf[z * ROWS + t * 5 + 3];
+		}
+#pragma unroll
+		for(int z = 0; z < TPI; z++) {
+			aes_encrypt(AesConstKey(P.hash), lb, x[z][0], x[z][1], x[z][2], x[z][3], h0[z]);
+			if(ROLE == 1) aes_encrypt(AesConstKey(P.hash), lb, x[z][0] ^ P.delta[0], x[z][1] ^ P.delta[1], x[z][2] ^ P.delta[2], x[z][3] ^ P.delta[3], h1[z]);
+		}
+#pragma unroll
+		for(int z = 0; z < TPI; z++) {
+			const uint64_t tile = tile0 + z;
+			if(tile >= P.tiles) continue;
+			const W pad0 = sizeof(W) == 8 ? (W) ((((uint64_t) (h0[z][1] ^ x[z][1])) << 32) | (h0[z][0] ^ x[z][0])) : (W) (h0[z][0] ^ x[z][0]);
+			if(ROLE == 0) {
+				__stcs(reinterpret_cast<W *>(P.pads) + tile * 128 + t, pad0);
+			} else {
+				const uint32_t y0 = x[z][0] ^ P.delta[0], y1 = x[z][1] ^ P.delta[1];
+				const W pad1 = sizeof(W) == 8 ? (W) ((((uint64_t) (h1[z][1] ^ y1)) << 32) | (h1[z][0] ^ y0)) : (W) (h1[z][0] ^ y0);
+				const uint64_t ni = tile * 128 + t, k = ni / WB;
+				const int bit = (int) (ni % WB);
+				if(k < P.n_rows) {
+					const W opt1 = (W) (xk[z] << bit) + pad0; // (1 << bit) * x + opt0, src/phase1.c:50
+					__stcs(reinterpret_cast<W *>(P.c) + ni, (W) (opt1 ^ pad1));
+					dot -= (uint64_t) pad0;             // share = -sum opt0, src/phase1.c:66-68
+				}
 			}
 		}
 	}
@@ -305,9 +355,10 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 		s->col_ptr = P.col;
 		s->n_rows = data->n;
 	}
-	size_t smem = AES_SMEM_BYTES + COT_GROUPS * 128 * 5 * sizeof(uint32_t);  // key schedules live in the gap below the tables
-	static_assert(2 * 44 * 128 * 4 <= AES_SMEM_GAP, "key schedules must fit below the AES tables");
-	uint64_t grid = (P.tiles + COT_GROUPS - 1) / COT_GROUPS;
+	size_t smem = AES_SMEM_BYTES;                         // the transposed rows live in the gap below the tables
+	static_assert(COT_GROUPS * 2 * 2 * 128 * 5 * 4 <= AES_SMEM_GAP, "transpose rows must fit below the AES tables");
+	constexpr int TPI = ROLE == 1 ? 2 : 1;
+	uint64_t grid = (P.tiles + COT_GROUPS * TPI - 1) / (COT_GROUPS * TPI);
 	int per_sm = 0;
 	if(s->bits == 64) {
 		P1_CUDA(cudaFuncSetAttribute(k_cot_tiles<uint64_t, ROLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));

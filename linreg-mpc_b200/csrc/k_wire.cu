@@ -296,7 +296,8 @@ __global__ void __launch_bounds__(WR_THREADS) k_unpack_count(const UnpackParams 
 	const uint32_t rm = up_range_mask(base, ps, pe);
 	if(rm) {
 		const uint4 a = __ldg(reinterpret_cast<const uint4 *>(m + base));
-		const uint4 b = __ldg(reinterpret_cast<const uint4 *>(m + base + 16));
+		// the stride is a multiple of 16, not of 32: the second half of the last 32-byte group may lie past the buffer
+		const uint4 b = base + 32 <= P.stride ? __ldg(reinterpret_cast<const uint4 *>(m + base + 16)) : make_uint4(0, 0, 0, 0);
 		if(rm == 0xffffffffu) {
 			cnt = __popc(~a.x & 0x80808080u) + __popc(~a.y & 0x80808080u) + __popc(~a.z & 0x80808080u) + __popc(~a.w & 0x80808080u)
 				+ __popc(~b.x & 0x80808080u) + __popc(~b.y & 0x80808080u) + __popc(~b.z & 0x80808080u) + __popc(~b.w & 0x80808080u);

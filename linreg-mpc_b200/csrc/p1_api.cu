@@ -64,6 +64,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->bits_p2 = ring_bits_p2;
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->launches = 0;
+	for(int i = 0; i < 8; i++) ctx->marks[i] = NULL;
 	ctx->pin_bytes = ctx->scratch_bytes = 4u << 20;
 	ctx->stage[0] = ctx->stage[1] = NULL;
 	ctx->stage_bytes = 0;
@@ -109,6 +110,7 @@ extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 	for(auto e : ctx->prof_pool) cudaEventDestroy(e);
 	cudaFree(ctx->scratch);
 	cudaFreeHost(ctx->pin);
+	for(int i = 0; i < 8; i++) if(ctx->marks[i]) cudaEventDestroy(ctx->marks[i]);
 	cudaEventDestroy(ctx->ev);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
@@ -132,6 +134,21 @@ extern "C" int p1_ctx_wait(p1_ctx *waiter, p1_ctx *signaler) {
 	std::lock_guard<std::mutex> l(waiter->mu);
 	P1_CUDA(cudaSetDevice(waiter->device));
 	P1_CUDA(cudaStreamWaitEvent(waiter->stream, signaler->ev, 0));
+	return 0;
+}
+
+extern "C" int p1_ctx_mark(p1_ctx *ctx, int slot) {
+	P1_ENTER(ctx);
+	P1_CHECK(slot >= 0 && slot < 8, "p1_ctx_mark: slot %d out of range [0,8)", slot);
+	if(!ctx->marks[slot]) P1_CUDA(cudaEventCreateWithFlags(&ctx->marks[slot], cudaEventDisableTiming));
+	P1_CUDA(cudaEventRecord(ctx->marks[slot], ctx->stream));
+	return 0;
+}
+
+extern "C" int p1_ctx_mark_sync(p1_ctx *ctx, int slot) {
+	P1_CHECK(ctx && slot >= 0 && slot < 8 && ctx->marks[slot], "p1_ctx_mark_sync: no mark %d on this context", slot);
+	// no context lock: another thread may keep enqueueing work while this one waits
+	P1_CUDA(cudaEventSynchronize(ctx->marks[slot]));
 	return 0;
 }
 
@@ -250,6 +267,11 @@ extern "C" int p1_host_free(p1_ctx *ctx, void *host) {
 extern "C" int p1_copy_h2d(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
 	P1_ENTER(ctx);
 	P1_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+	return 0;
+}
+extern "C" int p1_copy_d2h_async(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
+	P1_ENTER(ctx);
+	P1_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	return 0;
 }
 extern "C" int p1_copy_d2h(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {

@@ -17,6 +17,7 @@ struct p1_ctx {
 	int sm_count;
 	cudaStream_t stream;
 	cudaEvent_t ev;
+	cudaEvent_t marks[8];               // p1_ctx_mark / p1_ctx_mark_sync
 	std::mutex mu;
 	uint64_t launches;
 	// small pinned + device scratch for index arrays passed from the host

@@ -44,6 +44,9 @@ SIGNATURES = {
     "p1_host_free": (c_i, [c_vp, c_vp]),
     "p1_copy_h2d": (c_i, [c_vp, c_vp, c_vp, c_sz]),
     "p1_copy_d2h": (c_i, [c_vp, c_vp, c_vp, c_sz]),
+    "p1_copy_d2h_async": (c_i, [c_vp, c_vp, c_vp, c_sz]),
+    "p1_ctx_mark": (c_i, [c_vp, c_i]),
+    "p1_ctx_mark_sync": (c_i, [c_vp, c_i]),
     "p1_encode": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, c_d, c_i, ctypes.POINTER(c_vp)]),
     "p1_data_from_words": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, ctypes.POINTER(c_vp)]),
     "p1_data_free": (None, [c_vp]),
@@ -76,6 +79,38 @@ SIGNATURES = {
     "p1_probe_tensor_i8": (c_i, [c_vp, c_i, c_d, ctypes.POINTER(c_d), ctypes.POINTER(c_d), ctypes.POINTER(c_u64)]),
     "p1_finalize": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_i, c_i, c_d, c_vp, c_vp,
                           ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
+    "p1_group_create": (c_i, [c_vp, c_i, c_i, c_i, ctypes.POINTER(c_vp)]),
+    "p1_group_destroy": (None, [c_vp]),
+    "p1_group_size": (c_i, [c_vp]),
+    "p1_group_ctx": (c_vp, [c_vp, c_i]),
+    "p1_group_rows": (None, [c_vp, c_sz, c_i, ctypes.POINTER(c_sz), ctypes.POINTER(c_sz)]),
+    "p1_group_set_option": (c_i, [c_vp, c_cp, ctypes.c_long]),
+    "p1_group_sync": (c_i, [c_vp]),
+    "p1_group_launches": (c_u64, [c_vp]),
+    "p1_group_encode": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, c_d, c_i, ctypes.POINTER(c_vp)]),
+    "p1_gdata_free": (None, [c_vp]),
+    "p1_gdata_shard": (c_vp, [c_vp, c_i]),
+    "p1_group_acc_reset": (c_i, [c_vp, c_sz]),
+    "p1_group_acc_dev": (c_vp, [c_vp, c_i]),
+    "p1_group_reduce": (c_i, [c_vp]),
+    "p1_group_local_block": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, c_i]),
+    "p1_gvec_alloc": (c_i, [c_vp, c_sz, c_sz, ctypes.POINTER(c_vp)]),
+    "p1_gvec_free": (None, [c_vp]),
+    "p1_gvec_dev": (c_vp, [c_vp, c_i, ctypes.POINTER(c_sz)]),
+    "p1_gvec_gather": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz]),
+    "p1_gvec_scatter": (c_i, [c_vp, c_vp, c_sz, c_sz, c_vp]),
+    "p1_group_ti_generate": (c_i, [c_vp, c_cp, c_u64, c_sz, c_sz, c_vp, c_vp, c_vp, c_vp]),
+    "p1_group_party_b_mask": (c_i, [c_vp, c_vp, c_vp, c_sz, c_vp, c_vp]),
+    "p1_group_party_a_step": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_vp, c_vp]),
+    "p1_group_party_b_share": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "p1_group_acc_sub_values": (c_i, [c_vp, c_sz, c_vp, c_vp, c_sz]),
+    "p1_group_cot_sender_new": (c_i, [c_vp, c_cp, c_vp, ctypes.POINTER(c_vp)]),
+    "p1_group_cot_receiver_new": (c_i, [c_vp, c_vp, c_vp, ctypes.POINTER(c_vp)]),
+    "p1_group_cot_free": (None, [c_vp]),
+    "p1_group_cot_receiver_extend": (c_i, [c_vp, c_vp, c_vp, c_i32, c_vp]),
+    "p1_group_cot_sender_step": (c_i, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i64]),
+    "p1_group_cot_receiver_finish": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "p1_group_finalize": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, c_i, c_i, c_d, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
     "p1_msg_max_bytes": (c_sz, [c_vp, c_sz]),
     "p1_msg_pack": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp]),
     "p1_msg_unpack": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz, c_sz, c_vp, c_sz, c_vp, c_vp]),

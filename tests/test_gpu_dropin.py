@@ -84,3 +84,69 @@ def test_run_party_medium_instance_default_batch(p1lib, tmp_path):
     (rs, _, rsent), (gs, _, gsent) = both(path, d, len(cs), 64, 64, 56, 0, False)
     assert np.array_equal(gs, rs)
     assert np.array_equal(gsent, rsent)
+
+
+def _devices(k):
+    """k members for P1GPU_DEVICES: distinct GPUs when the box has them, else the same GPU k times (two
+    contexts and two row slabs on one device: the sharding logic runs on the regular one-GPU box)"""
+    import torch
+    n = torch.cuda.device_count()
+    return ",".join(str(g if n >= k else 0) for g in range(k))
+
+
+@pytest.mark.parametrize("ndev", [2, 3])
+@pytest.mark.parametrize("b1,b2,prec,prec2", CASES)
+def test_run_party_row_sharded_over_devices(p1lib, tmp_path, monkeypatch, ndev, b1, b2, prec, prec2):
+    """P1GPU_DEVICES lists several devices: run_party / run_trusted_initializer shard the rows over them behind
+    the unchanged entry points (p1_group); shares and bytes per socket still equal the reference's"""
+    monkeypatch.setenv("P1GPU_DEVICES", _devices(ndev))
+    monkeypatch.setenv("P1GPU_BATCH", "3")
+    n, d, cs = 2100, 12, [0, 4, 8]
+    X, y, _ = po.generate_lin_regression(n, d, seed=25)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, rsent), (gs, _, gsent) = both(path, d, len(cs), b1, b2, prec, prec2, False)
+    assert np.array_equal(gs, rs)
+    assert np.array_equal(gsent, rsent), "bytes per socket differ from the reference's"
+
+
+@pytest.mark.parametrize("b1,b2,prec,prec2", CASES)
+def test_run_party_use_ot_row_sharded_over_devices(p1lib, tmp_path, monkeypatch, b1, b2, prec, prec2):
+    monkeypatch.setenv("P1GPU_DEVICES", _devices(2))
+    n, d, cs = 900, 5, [0, 2, 4]
+    X, y, _ = po.generate_lin_regression(n, d, seed=26)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, _), (gs, _, _) = both(path, d, len(cs), b1, b2, prec, prec2, True)
+    assert np.array_equal(gs, rs)
+
+
+def test_run_party_sequential_diagonal_row_sharded(p1lib, tmp_path, monkeypatch):
+    """large values: the sequential double diagonal chained over two row slabs in device order"""
+    monkeypatch.setenv("P1GPU_DEVICES", _devices(2))
+    n, d, cs = 700, 6, [0, 3]
+    X, y, _ = po.generate_lin_regression(n, d, seed=27)
+    X *= 300.0
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    (rs, _, _), (gs, _, _) = both(path, d, len(cs), 64, 64, 56, 0, False)
+    assert np.array_equal(gs, rs)
+
+
+def test_run_party_accepts_tokens_the_gpu_parser_defers(p1lib, tmp_path):
+    """fscanf("%lf") accepts hex floats, more than 19 digits and infinities; the GPU parser defers them and the
+    host file converts them with strtod (src/linear.c:46,82): same shares as the reference"""
+    n, d, cs = 64, 4, [0, 2]
+    X, y, _ = po.generate_lin_regression(n, d, seed=28)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    text = open(path).read().split("\n")
+    row = text[6].split()            # first row of X (after "n d p", 2 + 2 endpoint lines, "n d")
+    row[0] = float(X[0, 0]).hex()
+    row[1] = "%.30f" % X[0, 1]
+    X[0, 1] = float(row[1])
+    row[2] = "inf"
+    text[6] = " ".join(row)
+    open(path, "w").write("\n".join(text))
+    (rs, _, _), (gs, _, _) = both(path, d, len(cs), 64, 64, 56, 0, False)
+    assert np.array_equal(gs, rs)

@@ -2,7 +2,9 @@
 """Isolated timings of single libp1gpu.so calls (tuning aid; bench.py is the judged harness).
 
   python tools/kbench.py ti     --n 1000000 --pairs 33 [--bits 64] [--opt ti_threads=512]
+  python tools/kbench.py fused  --n 1000000 --pairs 128       (the one-kernel masking loop, p1_masking_fused)
   python tools/kbench.py party  --n 1000000 --pairs 33
+  python tools/kbench.py probe                                 (dense int8 tcgen05 peak, N = 256 / 192 / 64)
   python tools/kbench.py gram   --n 1000000 --cols 500 --algo tcgen05|imad [--target]
   python tools/kbench.py encode --n 1000000 --cols 500
   python tools/kbench.py cot    --n 65536
@@ -28,7 +30,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ti", "party", "gram", "encode", "cot", "wire", "text"])
+    ap.add_argument("what", choices=["ti", "fused", "party", "gram", "encode", "cot", "wire", "text", "probe"])
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=33)
     ap.add_argument("--cols", type=int, default=500)
@@ -99,6 +101,30 @@ def main():
         ks = B * (2 * n * w + 16)
         res.update(ms=ms, pairs=B, keystream_GBs=ks / ms / 1e6, aes_blocks_per_s=ks / 16 / (ms * 1e-3),
                    clk_per_warp_block=148 * 1.965e9 * (ms * 1e-3) / (ks / 16 / 32))
+    elif args.what == "fused":
+        data, _, _, _ = encoded(n, 64)
+        mb = torch.empty(B * ld, dtype=wdt, device=dev)
+        ma = torch.empty(B * ld, dtype=wdt, device=dev)
+        xy = torch.zeros(B, dtype=torch.int64, device=dev)
+        r = torch.zeros(B, dtype=torch.int64, device=dev)
+        acc = torch.zeros(int(lib.p1_acc_len(64)), dtype=torch.int64, device=dev)
+        cols_b = torch.arange(B, dtype=torch.int32, device=dev) % 32
+        cols_a = torch.full((B,), 40, dtype=torch.int32, device=dev)       # one row i, j sweeps (as a run of the schedule)
+        sa = torch.arange(B, dtype=torch.int64, device=dev)
+        sb = torch.arange(B, dtype=torch.int64, device=dev) + 300
+        torch.cuda.synchronize()
+        key = bytes(range(16))
+        ms = timeit(lambda: lib.check(lib.p1_masking_fused(ctx, key, 0, B, n, 0, data, ptr(cols_a), ptr(cols_b), ptr(sa), ptr(sb),
+                                                           ptr(mb), ptr(ma), ld, None, None, ptr(xy), ptr(r), ptr(acc))))
+        ks = B * (2 * n * w + 16)
+        res.update(ms=ms, pairs=B, us_per_pair=ms * 1e3 / B, keystream_GBs=ks / ms / 1e6, aes_blocks_per_s=ks / 16 / (ms * 1e-3),
+                   hbm_GBs_algorithmic=B * 4 * n * w / ms / 1e6, lds_bound_frac_at_1965MHz=(ks / 16 / (ms * 1e-3)) / (148 * 32 * 1.965e9 / 135))
+        lib.p1_data_free(data)
+    elif args.what == "probe":
+        for ncols in (256, 192, 128, 64):
+            tops, ms = ctypes.c_double(), ctypes.c_double()
+            lib.check(lib.p1_probe_tensor_i8(ctx, ncols, 300.0, ctypes.byref(tops), ctypes.byref(ms), None))
+            res["n%d_tops" % ncols] = tops.value
     elif args.what == "party":
         data, _, _, _ = encoded(n, 64)
         bufs = [torch.empty(B * ld, dtype=wdt, device=dev).random_() for _ in range(4)]
