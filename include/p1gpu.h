@@ -382,7 +382,7 @@ int p1_parse_doubles(p1_ctx *ctx, const char *text, size_t bytes, double *out_de
  * on device 0; option "reduce" = 1: ncclAllReduce(ncclUint64, ncclSum) from the system libnccl.so.2).
  * The devices must have peer access to each other.  Listing one device twice is allowed (tests).
  * A group and everything made from it belong to one host thread at a time; the per-peer threads of OT
- * mode (src/phase1.c:503-513) each create their own group and may share one p1_gdata (read only). */
+ * mode (src/phase1.c:503-513) each create their own group and may share one p1_gdata, which they only read. */
 typedef struct p1_group p1_group;
 typedef struct p1_gdata p1_gdata;     /* encoded X, y as one p1_data per device */
 typedef struct p1_gvec p1_gvec;       /* a batch of n-row vectors as row slices on the devices */

@@ -123,7 +123,8 @@ def test_dropin_host_file_exports_the_reference_entry_points():
         defined = {l.split()[-1] for l in syms.splitlines() if " T " in l or " W " in l}
         undefined = {l.split()[-1] for l in syms.splitlines() if " U " in l}
         assert {"run_party", "run_trusted_initializer"} <= defined
-        assert {"p1_ti_generate", "p1_msg_pack", "p1_msg_unpack", "p1_parse_doubles", "p1_encode", "p1_finalize",
-                "p1_party_a_step", "p1_cot_sender_step"} <= undefined
+        assert {"p1_group_create", "p1_ti_generate", "p1_group_ti_generate", "p1_msg_pack", "p1_msg_unpack", "p1_parse_doubles",
+                "p1_group_encode", "p1_group_finalize", "p1_party_a_step", "p1_group_party_a_step", "p1_group_local_block",
+                "p1_group_cot_sender_step", "p1_group_cot_receiver_extend"} <= undefined
         lib = ctypes.CDLL(path)     # resolves libp1gpu.so through its rpath; needs no GPU to load
         assert lib.run_party is not None and lib.run_trusted_initializer is not None
