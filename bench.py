@@ -332,7 +332,8 @@ def main():
     torch.cuda.synchronize()
 
     gram = {"auto": pkg.ffi.P1_GRAM_AUTO, "imad": pkg.ffi.P1_GRAM_IMAD, "tcgen05": pkg.ffi.P1_GRAM_TCGEN05}[args.gram]
-    batch = args.batch_pairs or max(1, min(256, (256 << 20) // max(1, n_rows * w)))   # ~256 MB per message buffer
+    # pairs per launch: the fused loop keeps two message buffers per pipe (<= 1 GB each), the split kernels four (<= 256 MB each)
+    batch = args.batch_pairs or max(1, min(256, ((1 << 30) if args.aggregation == "masking" else (256 << 20)) // max(1, n_rows * w)))
     box = Phase1Box(lib, n, d, cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
                     row0=row0, n_rows=n_rows, batch_pairs=batch, pipes=args.pipes, gram_algo=gram, group=group)
     for o in args.opt:
@@ -402,13 +403,19 @@ def main():
     shares = None
     for _ in range(max(args.warmup, 3)):
         shares = step(Xd, yd)
-    for c in box.ctxs:
-        lib.check(lib.p1_ctx_profile(c, 1))
     launches0 = box.launches()
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step, ms_wall = timed(lambda: step(Xd, yd), args.steps)
     clocks = sampler.stop() if sampler else None
     launches = (box.launches() - launches0) // max(args.steps, 1)
+    # ---- per-kernel table: ONE more step with every launch bracketed by CUDA events, on a single pipe.  (In the timed
+    # steps above two pipes keep two persistent kernels in flight; an event bracket around one of them would include the
+    # time it waits for the other's SMs, so the brackets are taken with the kernels back to back on one stream.)
+    box.pipe_limit = 1
+    step(Xd, yd)
+    for c in box.ctxs:
+        lib.check(lib.p1_ctx_profile(c, 1))
+    ms_prof, _ = timed(lambda: step(Xd, yd), 1)
     prof = {}
     for k in range(pkg.ffi.P1_K_COUNT):
         tot, cnt = 0.0, 0
@@ -418,10 +425,10 @@ def main():
             tot += ms.value
             cnt += nl.value
         if cnt:
-            prof[lib.p1_kernel_class_name(k).decode()] = {"ms_per_step": tot / args.steps, "launches_per_step": cnt / args.steps,
-                                                         "avg_ms": tot / cnt}
+            prof[lib.p1_kernel_class_name(k).decode()] = {"ms_per_step": tot, "launches_per_step": cnt, "avg_ms": tot / cnt}
     for c in box.ctxs:
         lib.check(lib.p1_ctx_profile(c, 0))
+    box.pipe_limit = None
 
     # ---- short steps: the same step repeated for >= min_sampled_s under the sampler, so that the clock record
     # has enough samples (a 3 ms step x 5 is shorter than any sampling period) and the rate is a sustained one
@@ -627,7 +634,10 @@ def main():
                                   % ((d + 1) * nb / 1e9, C * (2 if not use_ot else 3 * 8) * nb / 1e9)),
                 "ring_macs_per_step": macs, "share_time_ms": ms_step, "wall_ms_per_step": ms_wall,
                 "gram_p1_equiv_macs": macs_gram_p1,
-                "gpu_launches": int(launches) * world, "kernels": kernels, "roofline": roofline, "clocks": clocks,
+                "gpu_launches": int(launches) * world, "kernels": kernels,
+                "kernels_note": "per-launch CUDA events of one extra step on a single pipe (%.1f ms: kernels back to back on one stream, "
+                                "event overhead included); the timed steps run %d pipes" % (ms_prof, args.pipes),
+                "roofline": roofline, "clocks": clocks,
                 "sustained": sustained, "int8_peak_probe": int8,
                 "e2e": e2e, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
         if wire:

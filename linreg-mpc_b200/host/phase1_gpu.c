@@ -68,12 +68,8 @@ __attribute__((weak)) int p1host_ti_key(uint8_t key[16]) {
  * 0 = receiver (gets seeds0 = k_i^0 and seeds1 = k_i^1).  Parties are 0-based node indices.
  * The default is in host/base_ot.c (Chou-Orlandi base OTs over the peer socket); a build against
  * Obliv-C may override it with the npot glue of INTEGRATION.md. */
-__attribute__((weak)) int p1host_base_ot(ProtocolDesc *pd, int sender_party, int receiver_party, int role,
-	uint8_t seeds0[128][16], uint8_t seeds1[128][16], uint8_t delta[16]) {
-	(void) pd; (void) sender_party; (void) receiver_party; (void) role; (void) seeds0; (void) seeds1; (void) delta;
-	fprintf(stderr, "p1host_base_ot: link host/base_ot.c (or the Obliv-C npot glue of INTEGRATION.md) to use --use_ot\n");
-	return 1;
-}
+int p1host_base_ot(ProtocolDesc *pd, int sender_party, int receiver_party, int role,
+	uint8_t seeds0[128][16], uint8_t seeds1[128][16], uint8_t delta[16]);
 
 /* devices of this party's group: P1GPU_DEVICES = "0,1,.." or the single device P1GPU_DEVICE (default 0) */
 __attribute__((weak)) int p1host_devices(int *devs, int max) {

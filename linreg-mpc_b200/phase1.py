@@ -147,6 +147,7 @@ class Phase1Box:
         self.sched = Schedule(d, col_start)
         self.acc_len = int(lib.p1_acc_len(d))
         self.batch_pairs = int(batch_pairs)
+        self.pipe_limit = None          # use only the first k pipes (bench.py's per-kernel pass: one stream, kernels back to back)
         self.dev = torch.device("cuda", device)
         self.ctxs = []
         for _ in range(max(1, pipes)):
@@ -281,7 +282,7 @@ class Phase1Box:
         self._fan_out()
         for b, q0 in enumerate(range(0, C, self.batch_pairs)):
             B = min(self.batch_pairs, C - q0)
-            pipe = b % len(self.ctxs)
+            pipe = b % (self.pipe_limit or len(self.ctxs))
             ctx = self.ctxs[pipe]
             xb, yb, mb, ma = (c_vp(tn.data_ptr()) for tn in self.bufs[pipe])
             xy = c_vp(self.xy.data_ptr() + 8 * q0)
@@ -413,7 +414,7 @@ class Phase1Box:
         products (bench samples).  Returns the number of inner products executed."""
         L, t = self.lib, self.torch
         ctx0 = self.ctxs[0]
-        npipe = len(self.ctxs)
+        npipe = self.pipe_limit or len(self.ctxs)
         u_bytes = int(L.p1_cot_u_bytes(ctx0, self.n_rows))
         c_bytes = int(L.p1_cot_c_bytes(ctx0, self.n_rows))
         if getattr(self, "_ot_bufs", None) is None:
@@ -429,7 +430,7 @@ class Phase1Box:
             seeds0, seeds1, delta = derive_cot_session(ot_key, ps + 2, pr + 2)
             chosen = np.ascontiguousarray(np.where(_bits128(delta)[:, None], seeds1, seeds0))
             sess = []
-            for ctx in self.ctxs:
+            for ctx in self.ctxs[:npipe]:
                 snd, rcv = c_vp(), c_vp()
                 L.check(L.p1_cot_sender_new(ctx, delta.tobytes(), ptr(chosen), ctypes.byref(snd)))
                 L.check(L.p1_cot_receiver_new(ctx, ptr(seeds0), ptr(seeds1), ctypes.byref(rcv)))
@@ -448,7 +449,7 @@ class Phase1Box:
                         L.check(L.p1_cot_advance(s2, self.n_total, 1))
                         L.check(L.p1_cot_advance(r2, self.n_total, 1))
                 done += 1
-            for ctx, (snd, rcv) in zip(self.ctxs, sess):
+            for ctx, (snd, rcv) in zip(self.ctxs[:npipe], sess):
                 L.check(L.p1_ctx_sync(ctx))
                 L.p1_cot_free(snd)
                 L.p1_cot_free(rcv)

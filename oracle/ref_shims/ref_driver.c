@@ -158,3 +158,41 @@ int p1ref_run(const char *path, int precision, int precision_p2, int use_ot,
 	free(th);
 	return status;
 }
+
+/* ---- self-test of the drop-in's default base-OT provider (linreg-mpc_b200/host/base_ot.c), present only in
+ * the gpuhost build: both roles as two threads over one loop-back connection */
+#ifdef P1_WITH_BASE_OT_SELFTEST
+int p1host_base_ot_co15(ProtocolDesc *pd, int sender_party, int receiver_party, int role,
+	uint8_t seeds0[128][16], uint8_t seeds1[128][16], uint8_t delta[16]);
+
+typedef struct {
+	ProtocolDesc *pd;
+	int role, status;
+	uint8_t (*s0)[16], (*s1)[16], *delta;
+} bot_args;
+
+static void *bot_main(void *v) {
+	bot_args *a = v;
+	a->status = p1host_base_ot_co15(a->pd, 3, 2, a->role, a->s0, a->s1, a->delta);
+	return NULL;
+}
+
+/* recv_s0 / recv_s1: the extension receiver's k_i^0, k_i^1; send_s: the extension sender's k_i^{Delta_i}; delta: its choice string */
+int p1ref_base_ot_selftest(uint8_t recv_s0[128][16], uint8_t recv_s1[128][16], uint8_t send_s[128][16], uint8_t delta[16]) {
+	p1shim_pipe *ab = p1shim_pipe_new(1 << 16), *ba = p1shim_pipe_new(1 << 16);
+	ProtocolDesc *pa = p1shim_pd_new(ab, ba, 0, 1), *pb = p1shim_pd_new(ba, ab, 1, 0);
+	uint8_t dummy_delta[16], dummy_s1[128][16];
+	bot_args ra = {.pd = pa, .role = 0, .s0 = recv_s0, .s1 = recv_s1, .delta = dummy_delta};
+	bot_args sa = {.pd = pb, .role = 1, .s0 = send_s, .s1 = dummy_s1, .delta = delta};
+	pthread_t t0, t1;
+	pthread_create(&t0, NULL, bot_main, &ra);
+	pthread_create(&t1, NULL, bot_main, &sa);
+	pthread_join(t0, NULL);
+	pthread_join(t1, NULL);
+	free(pa);
+	free(pb);
+	p1shim_pipe_free(ab);
+	p1shim_pipe_free(ba);
+	return ra.status | sa.status;
+}
+#endif

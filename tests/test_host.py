@@ -128,3 +128,60 @@ def test_dropin_host_file_exports_the_reference_entry_points():
                 "p1_group_cot_sender_step", "p1_group_cot_receiver_extend"} <= undefined
         lib = ctypes.CDLL(path)     # resolves libp1gpu.so through its rpath; needs no GPU to load
         assert lib.run_party is not None and lib.run_trusted_initializer is not None
+
+
+def test_default_base_ot_provider_of_the_dropin():
+    """linreg-mpc_b200/host/base_ot.c, the hook behind honestOTExt{Sender,Recver}New (src/phase1.c:394,397) in the
+    drop-in host file: SHA-256 against hashlib, the Edwards25519 ladder against big-integer arithmetic, and the
+    Chou-Orlandi exchange itself over a loop-back connection - the extension sender ends up with exactly
+    k_i^{Delta_i} of the receiver's pairs and with nothing that matches the other key"""
+    import ctypes
+    import hashlib
+    path = os.path.join(ROOT, "oracle", "_ref", "libp1gpuhost_64_64.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libp1gpuhost_* is built only where the reference sources are present")
+    L = ctypes.CDLL(path)
+    rng = np.random.default_rng(3)
+    for n in (0, 3, 55, 56, 63, 64, 65, 300):
+        msg = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        out = (ctypes.c_uint8 * 32)()
+        L.p1host_sha256(msg, len(msg), out)
+        assert bytes(out) == hashlib.sha256(msg).digest()
+    p = 2 ** 255 - 19
+    dd = (-121665 * pow(121666, -1, p)) % p
+
+    def add(P, Q):
+        (x1, y1), (x2, y2) = P, Q
+        t = dd * x1 * x2 * y1 * y2 % p
+        return ((x1 * y2 + x2 * y1) * pow(1 + t, -1, p) % p, (y1 * y2 + x1 * x2) * pow(1 - t, -1, p) % p)
+
+    def mul(s, P):
+        R = (0, 1)
+        while s:
+            if s & 1:
+                R = add(R, P)
+            P = add(P, P)
+            s >>= 1
+        return R
+    y = 4 * pow(5, -1, p) % p
+    x2 = (y * y - 1) * pow(dd * y * y + 1, -1, p) % p
+    x = pow(x2, (p + 3) // 8, p)
+    if (x * x - x2) % p:
+        x = x * pow(2, (p - 1) // 4, p) % p
+    if x & 1:
+        x = p - x
+    for _ in range(3):
+        s = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+        out = (ctypes.c_uint8 * 64)()
+        L.p1host_ed25519_scalarmult_base(s, out)
+        X, Y = mul(int.from_bytes(s, "little"), (x, y))
+        assert bytes(out) == X.to_bytes(32, "little") + Y.to_bytes(32, "little")
+    s0, s1, ss = (np.zeros((128, 16), np.uint8) for _ in range(3))
+    dl = np.zeros(16, np.uint8)
+    vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    assert L.p1ref_base_ot_selftest(vp(s0), vp(s1), vp(ss), vp(dl)) == 0
+    bits = np.unpackbits(dl, bitorder="little").astype(bool)
+    assert 20 < bits.sum() < 108
+    assert np.array_equal(np.where(bits[:, None], s1, s0), ss)
+    assert not np.any(np.all(np.where(bits[:, None], s0, s1) == ss, axis=1))
+    assert len({bytes(r) for r in np.concatenate([s0, s1])}) == 256
