@@ -271,6 +271,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in host file vs reference phase1.c timing (n=1M, d=10, 3 providers)")
     ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (p1_ctx_set_option), repeatable")
     ap.add_argument("--wire-sample", type=int, default=3300, help="cross pairs to time with GPU (de)serialisation of every message (0 = skip)")
     ap.add_argument("--ot-sample", type=int, default=8, help="masking workloads: inner products of the --use_ot path to time as a side figure (0 = skip)")
@@ -623,6 +624,15 @@ def main():
         smp.close()
 
     box.close()
+
+    # ---- the drop-in boundary itself (rank 0, N = 1): the reference's run_party / run_trusted_initializer entry points
+    # served by linreg-mpc_b200/host/phase1_gpu.c vs the reference's own phase1.c, same loop-back driver, same instance file
+    dropin = None
+    if rank == 0 and world == 1 and not args.no_dropin and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libp1gpuhost_64_64.so")):
+        from tools.dropin_timing import measure as dropin_measure
+        torch.cuda.empty_cache()
+        dropin = dropin_measure(1_000_000, 10, 3, use_ot=False, bits=64)
+
     if rank == 0:
         value = macs / (ms_step * 1e-3) / 1e9
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -639,7 +649,7 @@ def main():
                                 "event overhead included); the timed steps run %d pipes" % (ms_prof, args.pipes),
                 "roofline": roofline, "clocks": clocks,
                 "sustained": sustained, "int8_peak_probe": int8,
-                "e2e": e2e, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
+                "e2e": e2e, "e2e_dropin": dropin, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
         if wire:
             line["value_with_wire"] = wire["value_with_wire"]
         if use_ot:

@@ -127,6 +127,10 @@ int p1_ctx_mark_sync(p1_ctx *ctx, int slot);
  * statistics (max |word|, exact sum of squares) are gathered in the same pass. */
 int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n, size_t d,
               double normalizer, int precision, p1_data **out);
+/* a provider that runs the protocol again on new values of the same shape (bench.py's step; a service that
+ * re-fits as rows are corrected): the same pass into the store that an earlier call made - same n, d and
+ * presence of y - with no allocation and no host synchronisation, ordered on the context's stream */
+int p1_encode_again(p1_ctx *ctx, p1_data *data, const double *X, const double *y, double normalizer, int precision);
 /* same, from ring words that are already encoded (row-major n x d, and n) */
 int p1_data_from_words(p1_ctx *ctx, const void *X_words, const void *y_words, size_t n, size_t d,
                        p1_data **out);
@@ -313,6 +317,17 @@ int p1_finalize(p1_ctx *ctx, const uint64_t *acc, size_t d, size_t col_lo, size_
                 int precision, int precision_p2, double normalizer2,
                 const double *diag_xy, int *need_sequential,
                 void **res_A, void **res_b);
+
+/* The same tail for `num` providers at once, stream-ordered and without a host round trip (the short steps of
+ * cfg4 / cfg5, where a D2H plus a host loop per provider costs more than the kernels).  acc_dev: num accumulators
+ * of p1_acc_len(d) words, already combined over row shards; provider k owns the columns
+ * [col_start_dev[k], col_start_dev[k + 1]) (device array of num + 1 int32).  out_dev: num x (d(d+1)/2 + d) uint64
+ * words, res_A | res_b of provider k as ufixed_t widened to 64 bits (zero extended).  diag_xy_dev: d doubles
+ * indexed by column, or NULL; *need_dev counts the diagonal words whose exact shortcut does not apply and for
+ * which no xy was supplied (they are left 0 - the caller then falls back to p1_diag_sequential + the host call). */
+int p1_finalize_async(p1_ctx *ctx, const uint64_t *acc_dev, size_t num, size_t d, const int32_t *col_start_dev,
+                      int precision, int precision_p2, double normalizer2, const double *diag_xy_dev,
+                      int32_t *need_dev, uint64_t *out_dev);
 
 /* ------------------------------------------------------------------ f2: messages on the wire
  * SecureMultiplication__Msg (src/protobuf/secure_multiplication{,_32}.proto):

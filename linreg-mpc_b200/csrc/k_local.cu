@@ -198,3 +198,65 @@ int p1_launch_gram_imad(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t 
 	P1_LAUNCHED(ctx);
 	return 0;
 }
+
+// ------------------------------------------------------------------ finalize on the device
+
+// (fixed_t) / (fixed_p1_t) cast of a double as x86-64 cvttsd2si does it (src/fixed.c:3-5,11-13)
+__device__ __forceinline__ int64_t p1_cast_x86(double v, int bits) {
+	if(bits == 64) {
+		if(!(v >= -9223372036854775808.0 && v < 9223372036854775808.0)) return (int64_t) 0x8000000000000000ull;
+		return (int64_t) __double2ll_rz(v);
+	}
+	if(!(v > -2147483649.0 && v < 2147483648.0)) return (int64_t) (int32_t) 0x80000000u;
+	return (int64_t) __double2int_rz(v);
+}
+
+// One thread per share word of one provider: the tail of run_party (src/phase1.c:605-641) with the diagonal of the
+// owned columns taken from the exact statistics (or diag_xy) - the same arithmetic as p1_finalize, word for word.
+__global__ void __launch_bounds__(256) k_finalize(const uint64_t *__restrict__ acc, size_t num, size_t d, size_t nA,
+	const int32_t *__restrict__ col_start, int b1, int b2, int shift, double inv_scale, double scale, double normalizer2,
+	const double *__restrict__ diag_xy, int32_t *__restrict__ need, uint64_t *__restrict__ out) {
+	size_t per = nA + d, t = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if(t >= num * per) return;
+	size_t p = t / per, k = t - p * per;
+	const uint64_t *a = acc + p * (nA + 4 * d);
+	uint64_t v = a[k];
+	if(k < nA) {
+		// k = i (i + 1) / 2 + j, j <= i
+		size_t i = (size_t) ((sqrt(8.0 * (double) k + 1.0) - 1.0) * 0.5);
+		while(i * (i + 1) / 2 > k) i--;
+		while((i + 1) * (i + 2) / 2 <= k) i++;
+		size_t j = k - i * (i + 1) / 2;
+		if(j == i && (int32_t) i >= col_start[p] && (int32_t) i < col_start[p + 1]) {
+			uint64_t lo = a[nA + d + i], hi = a[nA + 2 * d + i], viol = a[nA + 3 * d + i];
+			// S = (hi << 32) + lo <= 2^53 ?
+			uint64_t S = (hi << 32) + lo;
+			bool exact = viol == 0 && (hi >> 32) == 0 && S >= (hi << 32) && S <= (1ull << 53);
+			double xy;
+			if(exact) xy = __dmul_rn((double) S, inv_scale);
+			else if(diag_xy && !isnan(diag_xy[i])) xy = diag_xy[i];
+			else {
+				atomicAdd(need, 1);
+				out[t] = 0;
+				return;
+			}
+			v = (uint64_t) p1_cast_x86(__dmul_rn(__ddiv_rn(xy, normalizer2), scale), b1);
+		}
+	}
+	if(b1 == 64 && b2 == 64) out[t] = v;
+	else if(b1 == 32) out[t] = (uint32_t) v;
+	else out[t] = (uint32_t) (((int64_t) v) >> shift); // src/phase1.c:617,633
+}
+
+int p1_launch_finalize(p1_ctx *ctx, const uint64_t *acc_dev, size_t num, size_t d, const int32_t *col_start_dev, int precision,
+	int precision_p2, double normalizer2, const double *diag_xy_dev, int32_t *need_dev, uint64_t *out_dev) {
+	size_t nA = p1_nA(d), total = num * (nA + d);
+	if(cudaMemsetAsync(need_dev, 0, sizeof(int32_t), ctx->stream) != cudaSuccess) return p1_fail("p1_finalize_async: memset failed");
+	if(!total) return 0;
+	double scale = (double) (1ll << precision);
+	p1_prof_begin(ctx, P1_K_DIAG);
+	k_finalize<<<(unsigned) ((total + 255) / 256), 256, 0, ctx->stream>>>(acc_dev, num, d, nA, col_start_dev, ctx->bits_p1, ctx->bits_p2,
+		precision - precision_p2, 1.0 / scale, scale, normalizer2, diag_xy_dev, need_dev, out_dev);
+	P1_LAUNCHED(ctx);
+	return 0;
+}

@@ -424,24 +424,8 @@ static int ensure_stage(p1_ctx *ctx, size_t bytes) {
 	return 0;
 }
 
-extern "C" int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n, size_t d,
-	double normalizer, int precision, p1_data **out) {
-	P1_ENTER(ctx);
-	P1_CHECK(out && X, "p1_encode: arguments may not be null");
-	*out = NULL;
-	P1_CHECK(n > 0 && d > 0, "p1_encode: empty matrix (%zu x %zu)", n, d);
-	P1_CHECK(precision >= 0 && precision < 63, "p1_encode: precision %d out of range", precision);
-	p1_data *dt = NULL;
-	// Digit planes for the tensor-core Gram, written in the same pass (saves k_limb_split's re-read of every
-	// word).  The digit count must be fixed before the data has been seen: enough for |value| <= 16 at this
-	// scale; if a block turns out to need more (statistics of this very pass), its Gram splits again itself.
-	int Lg = 0;
-	if(ctx->opt_encode_planes && n >= 4096) {
-		const double bound = 16.0 * (double) (1ll << precision) / normalizer;
-		if(bound < 9.0e15) Lg = p1_tc_digits((uint64_t) bound + 1, ctx->bits_p1 / 8);
-		if(Lg > 4) Lg = 0;
-	}
-	if(data_alloc(ctx, n, d, y != NULL, &dt, Lg)) return 1;
+// X / y (host or device) -> the column store of dt, on the context's stream
+static int encode_fill(p1_ctx *ctx, p1_data *dt, const double *X, const double *y, size_t n, size_t d, double normalizer, int precision) {
 	int st = 0;
 	if(p1_is_device_ptr(X)) {
 		st = p1_launch_encode(ctx, X, n, d, 0, NULL, normalizer, precision, dt);
@@ -475,12 +459,48 @@ extern "C" int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n
 		}
 		if(!st) st = p1_launch_encode(ctx, NULL, n, d, 0, y_dev, normalizer, precision, dt);
 	}
-	if(st) {
+	return st;
+}
+
+// digit planes for the tensor-core Gram, written in the encode pass (saves k_limb_split's re-read of every
+// word).  The digit count must be fixed before the data has been seen: enough for |value| <= 16 at this
+// scale; if a block turns out to need more (statistics of this very pass), its Gram splits again itself.
+static int encode_plane_digits(p1_ctx *ctx, size_t n, double normalizer, int precision) {
+	int Lg = 0;
+	if(ctx->opt_encode_planes && n >= 4096) {
+		const double bound = 16.0 * (double) (1ll << precision) / normalizer;
+		if(bound < 9.0e15) Lg = p1_tc_digits((uint64_t) bound + 1, ctx->bits_p1 / 8);
+		if(Lg > 4) Lg = 0;
+	}
+	return Lg;
+}
+
+extern "C" int p1_encode(p1_ctx *ctx, const double *X, const double *y, size_t n, size_t d,
+	double normalizer, int precision, p1_data **out) {
+	P1_ENTER(ctx);
+	P1_CHECK(out && X, "p1_encode: arguments may not be null");
+	*out = NULL;
+	P1_CHECK(n > 0 && d > 0, "p1_encode: empty matrix (%zu x %zu)", n, d);
+	P1_CHECK(precision >= 0 && precision < 63, "p1_encode: precision %d out of range", precision);
+	p1_data *dt = NULL;
+	if(data_alloc(ctx, n, d, y != NULL, &dt, encode_plane_digits(ctx, n, normalizer, precision))) return 1;
+	if(encode_fill(ctx, dt, X, y, n, d, normalizer, precision)) {
 		p1_data_free(dt);
 		return 1;
 	}
 	*out = dt;
 	return 0;
+}
+
+extern "C" int p1_encode_again(p1_ctx *ctx, p1_data *dt, const double *X, const double *y, double normalizer, int precision) {
+	P1_ENTER(ctx);
+	P1_CHECK(dt && X, "p1_encode_again: arguments may not be null");
+	P1_CHECK(dt->device == ctx->device && dt->bits == ctx->bits_p1, "p1_encode_again: the store belongs to another device or ring");
+	P1_CHECK((y != NULL) == dt->has_y, "p1_encode_again: the store was allocated %s a target column", dt->has_y ? "with" : "without");
+	P1_CHECK(precision >= 0 && precision < 63, "p1_encode_again: precision %d out of range", precision);
+	P1_CHECK(!dt->planes || dt->Lg == encode_plane_digits(ctx, dt->n, normalizer, precision), "p1_encode_again: the scale needs another digit count than the store holds");
+	P1_CUDA(cudaMemsetAsync(dt->stats, 0, dt->stat_bytes, ctx->stream));
+	return encode_fill(ctx, dt, X, y, dt->n, dt->d, normalizer, precision);
 }
 
 extern "C" int p1_data_from_words(p1_ctx *ctx, const void *Xw, const void *yw, size_t n, size_t d, p1_data **out) {
@@ -662,4 +682,13 @@ extern "C" int p1_finalize(p1_ctx *ctx, const uint64_t *acc, size_t d, size_t co
 	if(res_A) *res_A = A;
 	if(res_b) *res_b = B;
 	return 0;
+}
+
+extern "C" int p1_finalize_async(p1_ctx *ctx, const uint64_t *acc_dev, size_t num, size_t d, const int32_t *col_start_dev,
+	int precision, int precision_p2, double normalizer2, const double *diag_xy_dev, int32_t *need_dev, uint64_t *out_dev) {
+	P1_ENTER(ctx);
+	P1_CHECK(acc_dev && col_start_dev && need_dev && out_dev, "p1_finalize_async: arguments may not be null");
+	P1_CHECK(p1_is_device_ptr(acc_dev) && p1_is_device_ptr(col_start_dev) && p1_is_device_ptr(out_dev), "p1_finalize_async: device pointers expected");
+	P1_CHECK(precision >= 0 && precision < 63 && precision_p2 <= precision, "p1_finalize_async: invalid precision");
+	return p1_launch_finalize(ctx, acc_dev, num, d, col_start_dev, precision, precision_p2, normalizer2, diag_xy_dev, need_dev, out_dev);
 }

@@ -99,6 +99,8 @@ int p1_launch_gram_imad(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t 
 int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int owns_target, uint64_t *acc_dev);
 int p1_launch_diag_stats(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, uint64_t *acc_dev);
 int p1_launch_diag_seq(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t col_hi, int precision, double *xy_dev);
+int p1_launch_finalize(p1_ctx *ctx, const uint64_t *acc_dev, size_t num, size_t d, const int32_t *col_start_dev, int precision,
+	int precision_p2, double normalizer2, const double *diag_xy_dev, int32_t *need_dev, uint64_t *out_dev);
 
 // device helpers
 #ifdef __CUDACC__

@@ -94,6 +94,17 @@ __attribute__((weak)) int p1host_devices(int *devs, int max) {
 /* ------------------------------------------------------------------ small helpers */
 
 /* owner of a row as a 0-based node index; the target (row d) belongs to the last party (:25-33) */
+/* P1GPU_TRACE=1: one line per party on stderr with the seconds spent per stage (where does a run's time go) */
+static double now_s(void) {
+	struct timespec t;
+	clock_gettime(CLOCK_MONOTONIC, &t);
+	return (double) t.tv_sec + 1e-9 * (double) t.tv_nsec;
+}
+static int trace_on(void) {
+	const char *e = getenv("P1GPU_TRACE");
+	return e && atoi(e) > 0;
+}
+
 static int owner_of(size_t row, const config *c) {
 	int party = 0;
 	for(; party + 1 < c->num_parties && c->index_owned[party + 1] <= (ssize_t) row; party++);
@@ -321,6 +332,8 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 	uint64_t *xy_dev = NULL, *r_dev = NULL;
 	int status = 1;
 	if(use_ot) return 0;                 /* the TI takes no part in the OT variant (:256) */
+	double t_wait = 0, t_send = 0;
+	const double t_begin = now_s();
 	check(!gpu_init(&g, c->n, 2, 2), "could not set up the GPU");
 	uint8_t key[16];
 	check(!p1host_ti_key(key), "could not draw the PRG key");
@@ -336,7 +349,10 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 		/* the GPU works on the next run while this one goes out on the sockets */
 		const int have_next = next_run(&pc, c, g.batch, &nxt);
 		if(have_next) check(!ti_prepare(&g, key, c, &nxt, set ^ 1, xy_dev, r_dev), "could not prepare a run");
+		double t0 = now_s();
 		GCHECK(wire_ready(&g, set));
+		t_wait += now_s() - t0;
+		t0 = now_s();
 		const uint64_t *sa = sizes_host_at(&g, set, 0), *sb = sizes_host_at(&g, set, 1);
 		const uint8_t *wa = wire_host_at(&g, set, 0), *wb = wire_host_at(&g, set, 1);
 		for(size_t p = 0; p < cur.count; p++) {          /* the reference's order on the wire: a, b per pair (:281-284) */
@@ -346,10 +362,12 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 			check(!status, "Could not send message to party B (%d)", cur.owner_j);
 		}
 		status = 1;
+		t_send += now_s() - t0;
 		cur = nxt;
 		have = have_next;
 		set ^= 1;
 	}
+	if(trace_on()) fprintf(stderr, "p1gpu trace TI: waiting for the GPU %.3f  sending %.3f  total %.3f s, batch %zu\n", t_wait, t_send, now_s() - t_begin, g.batch);
 	status = 0;
 error:
 	if(g.ctx) {
@@ -548,10 +566,14 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 	check(me >= 2 && me < P, "run_party: party %d is not a data provider", c->party);
 	const size_t lo = (size_t) c->index_owned[me], hi = me < P - 1 ? (size_t) c->index_owned[me + 1] : d;
 
+	double t_ti = 0, t_peer = 0, t_gpu = 0, t_send = 0;
+	const double t_begin = now_s();
 	check(!gpu_init(&g, c->n, use_ot ? 0 : 3, use_ot ? 0 : 1), "could not set up the GPU");
+	const double t_init = now_s();
 	status = load_inputs(&g, c, precision, &data);
 	check(!status, "Could not read data");
 	status = 1;
+	const double t_loaded = now_s();
 	const size_t acc_len = p1_acc_len(d);
 
 	if(use_ot) {
@@ -605,7 +627,9 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 				cols[p] = r.owner_i == me ? (int32_t) r.i : (int32_t) j;           /* column d = the target vector */
 			}
 			/* random vectors and values from the TI (:170) */
+			double t0 = now_s(), t1;
 			check(!recv_to_device(&g, self->peer[0], count, g.vec[0], g.vals_dev), "Could not receive message from TI");
+			t_ti += (t1 = now_s()) - t0;
 			if(r.owner_i == me) {                                  /* party a (:173-196) */
 				ProtocolDesc *pb = self->peer[r.owner_j];
 				clock_gettime(CLOCK_MONOTONIC, &wait_start);
@@ -613,25 +637,31 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 				clock_gettime(CLOCK_MONOTONIC, &wait_end);
 				check(!status, "Could not receive message from party B (%d)", r.owner_j);
 				status = 1;
+				t_peer += (t0 = now_s()) - t1;
 				GCHECK(do_a_step(&g, data, cols, slots, count));           /* out = a - y, share += <b + x, y> */
 				check(!pack_start(&g, 0, 1, g.vec[2], g.zero_dev, count), "could not serialise the messages for party B");
 				GCHECK(wire_mark(&g, 0));
 				GCHECK(wire_ready(&g, 0));
+				t_gpu += (t1 = now_s()) - t0;
 				for(size_t p = 0; p < count; p++)
 					check(!send_wire(pb, wire_host_at(&g, 0, 1) + p * g.stride, sizes_host_at(&g, 0, 1)[p]), "Could not send message to party B (%d)", r.owner_j);
+				t_send += now_s() - t1;
 			} else {                                             /* party b (:198-224) */
 				ProtocolDesc *pa = self->peer[r.owner_i];
 				GCHECK(do_b_mask(&g, data, cols, count));                  /* out = b + x */
 				check(!pack_start(&g, 0, 1, g.vec[2], g.zero_dev, count), "could not serialise the messages for party A");
 				GCHECK(wire_mark(&g, 0));
 				GCHECK(wire_ready(&g, 0));
+				t_gpu += (t0 = now_s()) - t1;
 				for(size_t p = 0; p < count; p++)
 					check(!send_wire(pa, wire_host_at(&g, 0, 1) + p * g.stride, sizes_host_at(&g, 0, 1)[p]), "Could not send message to party A (%d)", r.owner_i);
+				t_send += (t1 = now_s()) - t0;
 				clock_gettime(CLOCK_MONOTONIC, &wait_start);
 				status = recv_to_device(&g, pa, count, g.vec[1], g.vals2_dev);
 				clock_gettime(CLOCK_MONOTONIC, &wait_end);
 				check(!status, "Could not receive message from party A (%d)", r.owner_i);
 				status = 1;
+				t_peer += now_s() - t1;
 				GCHECK(do_b_share(&g, data, cols, slots, count));          /* share += <a - y, b> */
 			}
 			GCHECK(p1_group_acc_sub_values(g.grp, d, slots, g.vals_dev, count));      /* share -= value (:196,222) */
@@ -649,6 +679,9 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 		if(res_A) *res_A = A; else free(A);
 		if(res_b) *res_b = B; else free(B);
 	}
+	if(trace_on()) fprintf(stderr, "p1gpu trace party %d: setup %.3f  inputs %.3f  protocol %.3f (from the TI %.3f, from the peer %.3f, "
+		"GPU + D2H %.3f, send %.3f)  total %.3f s, %d device(s), batch %zu\n", c->party, t_init - t_begin, t_loaded - t_init,
+		now_s() - t_loaded, t_ti, t_peer, t_gpu, t_send, now_s() - t_begin, g.ndev, g.batch);
 	status = 0;
 error:
 	if(g.grp) p1_group_sync(g.grp);

@@ -173,6 +173,16 @@ class Phase1Box:
         self.slot_b = to_dev(S.owner_j[cr].astype(np.int64) * self.acc_len + S.slot[cr], torch.int64)
         self.bufs = None
         self.normalizer = math.sqrt(math.pow(2, precision) * float(self.n_total))  # src/phase1.c:473
+        # one step is stream-ordered from reset() to the D2H of the shares: torch work (zeroing, the all-reduce over
+        # row shards) is issued on pipe 0's stream, so nothing in between needs the host
+        self.s0 = torch.cuda.ExternalStream(int(lib.p1_ctx_stream(self.ctxs[0])), device=self.dev)
+        self.col_start_dev = to_dev(np.asarray(list(col_start) + [self.d]), torch.int32)
+        self.out_dev = torch.zeros(S.num_dp * (S.nA + self.d), dtype=torch.int64, device=self.dev)
+        self.need_dev = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.out_host = torch.zeros(S.num_dp * (S.nA + self.d), dtype=torch.int64).pin_memory()
+        self.need_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._has_y = None
+        torch.cuda.current_stream(self.dev).synchronize()
 
     # ------------------------------------------------------------------
     def close(self):
@@ -202,9 +212,14 @@ class Phase1Box:
     # ------------------------------------------------------------------
     def encode(self, X, y):
         """X: this shard's rows (n_rows x d doubles; numpy = host, torch cuda tensor = device)."""
+        if self.data is not None and self._has_y == (y is not None):
+            # same shape as the last run: re-encode in place (no allocation, no host synchronisation)
+            self.lib.check(self.lib.p1_encode_again(self.ctxs[0], self.data, ptr(X), ptr(y), self.normalizer, self.precision))
+            return
         if self.data is not None:
             self.lib.p1_data_free(self.data)
             self.data = None
+        self._has_y = y is not None
         out = c_vp()
         self.lib.check(self.lib.p1_encode(self.ctxs[0], ptr(X), ptr(y), self.n_rows, self.d,
                                           self.normalizer, self.precision, ctypes.byref(out)))
@@ -214,10 +229,9 @@ class Phase1Box:
         self.ld = int(ld.value)
 
     def reset(self):
-        # torch's stream and ours are unrelated: order explicitly
-        self.flat.zero_()
-        self.r.zero_()
-        self.torch.cuda.current_stream(self.dev).synchronize()
+        with self.torch.cuda.stream(self.s0):
+            self.flat.zero_()
+            self.r.zero_()
 
     def local_blocks(self):
         S = self.sched
@@ -320,9 +334,8 @@ class Phase1Box:
         """exact ring combination of row shards: wrapping integer sum (NCCL over NVLink)"""
         if self.group is None:
             return
-        self.sync()
-        ring_all_reduce(self.flat, self.group)
-        self.torch.cuda.current_stream(self.dev).synchronize()
+        with self.torch.cuda.stream(self.s0):      # ordered behind the kernels, no host synchronisation
+            ring_all_reduce(self.flat, self.group)
 
     def apply_values(self):
         """share -= value, once, after the row shards were combined (src/phase1.c:196,222)"""
@@ -356,7 +369,20 @@ class Phase1Box:
 
     def finalize(self):
         """tail of run_party for every provider (src/phase1.c:605-641): returns
-        shares[num_dp, d(d+1)/2 + d] as ufixed_t widened to uint64."""
+        shares[num_dp, d(d+1)/2 + d] as ufixed_t widened to uint64.  One kernel for all providers behind the
+        all-reduce and one D2H; only a diagonal whose exact-integer shortcut does not apply (values far outside
+        [-1, 1]) sends the step through the host path with the sequential double sum."""
+        S, L, ctx = self.sched, self.lib, self.ctxs[0]
+        L.check(L.p1_finalize_async(ctx, ptr(self.acc), S.num_dp, self.d, ptr(self.col_start_dev), self.precision,
+                                    self.precision_p2, float(self.d), None, ptr(self.need_dev), ptr(self.out_dev)))
+        L.check(L.p1_copy_d2h_async(ctx, c_vp(self.out_host.data_ptr()), ptr(self.out_dev), self.out_host.numel() * 8))
+        L.check(L.p1_copy_d2h_async(ctx, c_vp(self.need_host.data_ptr()), ptr(self.need_dev), 4))
+        self.sync()
+        if int(self.need_host[0]) == 0:
+            return self.out_host.numpy().view(np.uint64).reshape(S.num_dp, S.nA + self.d).copy()
+        return self._finalize_host()
+
+    def _finalize_host(self):
         S, L = self.sched, self.lib
         self.sync()
         acc_host = self.acc.cpu().numpy().view(np.uint64).reshape(S.num_dp, self.acc_len)

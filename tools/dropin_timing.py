@@ -20,6 +20,39 @@ sys.path.insert(0, ROOT)
 from oracle import pyoracle as po  # noqa: E402
 
 
+def measure(n, d, providers, use_ot=False, bits=64, devices=None):
+    """one instance file through the drop-in host file (cold, then warm) and through the reference's phase1.c"""
+    prec = 56 if bits == 64 else 24
+    X, y, _ = po.generate_lin_regression(n, d, seed=31)
+    cs = po.even_col_start(d, providers)
+    path = os.path.join(tempfile.mkdtemp(), "inst.in")
+    po.Oracle().write_instance(path, X, y, cs)
+    if devices:
+        os.environ["P1GPU_DEVICES"] = devices
+    out = {"n": n, "d": d, "providers": providers, "use_ot": use_ot, "bits": bits,
+           "devices": os.environ.get("P1GPU_DEVICES", os.environ.get("P1GPU_DEVICE", "0")),
+           "text_bytes": os.path.getsize(path)}
+    res = {}
+    for name, gpuhost in (("gpu_host", True), ("gpu_host_warm", True), ("reference_phase1_c", False)):
+        lib = po.RefLib(bits, bits, gpuhost=gpuhost)
+        t0 = time.perf_counter()
+        shares, stats, sent = lib.run(path, d, providers, prec, 0, use_ot=use_ot)
+        res[name] = shares
+        out[name + "_s"] = time.perf_counter() - t0
+        out[name + "_bytes_on_sockets"] = int(sent.sum())
+    os.remove(path)
+    out["shares_identical"] = bool(np.array_equal(res["gpu_host_warm"], res["reference_phase1_c"]) and
+                                   np.array_equal(res["gpu_host"], res["reference_phase1_c"]))
+    out["speedup_warm"] = out["reference_phase1_c_s"] / out["gpu_host_warm_s"]
+    out["speedup_cold"] = out["reference_phase1_c_s"] / out["gpu_host_s"]
+    # every byte on a socket was copied off a GPU by its sender and onto one by its receiver; the inputs go up as text
+    out["h2d_bytes"] = out["text_bytes"] + out["gpu_host_warm_bytes_on_sockets"]
+    out["d2h_bytes"] = out["gpu_host_warm_bytes_on_sockets"] + int(res["gpu_host_warm"].size) * (bits // 8)
+    out["note"] = ("all parties (TI + providers) as threads of one process over the in-process loop-back transport of oracle/ref_shims; "
+                   "cold = first run of the process (CUDA context, library load), warm = second run")
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=100000)
@@ -27,25 +60,9 @@ def main():
     ap.add_argument("--providers", type=int, default=3)
     ap.add_argument("--use-ot", action="store_true")
     ap.add_argument("--bits", type=int, default=64)
+    ap.add_argument("--devices", default=None, help="P1GPU_DEVICES for the drop-in's parties, e.g. 0,1")
     args = ap.parse_args()
-    prec = 56 if args.bits == 64 else 24
-    X, y, _ = po.generate_lin_regression(args.n, args.d, seed=31)
-    cs = po.even_col_start(args.d, args.providers)
-    path = os.path.join(tempfile.mkdtemp(), "inst.in")
-    po.Oracle().write_instance(path, X, y, cs)
-    out = {"n": args.n, "d": args.d, "providers": args.providers, "use_ot": args.use_ot, "bits": args.bits,
-           "text_bytes": os.path.getsize(path)}
-    res = {}
-    for name, gpuhost in (("gpu_host", True), ("gpu_host_warm", True), ("reference_phase1_c", False)):
-        lib = po.RefLib(args.bits, args.bits, gpuhost=gpuhost)
-        t0 = time.perf_counter()
-        shares, stats, sent = lib.run(path, args.d, args.providers, prec, 0, use_ot=args.use_ot)
-        res[name] = shares
-        out[name + "_s"] = time.perf_counter() - t0
-        out[name + "_bytes_on_sockets"] = int(sent.sum())
-    out["shares_identical"] = bool(np.array_equal(res["gpu_host_warm"], res["reference_phase1_c"]))
-    out["speedup_warm"] = out["reference_phase1_c_s"] / out["gpu_host_warm_s"]
-    print(json.dumps(out))
+    print(json.dumps(measure(args.n, args.d, args.providers, args.use_ot, args.bits, args.devices)))
 
 
 if __name__ == "__main__":

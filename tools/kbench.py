@@ -30,7 +30,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ti", "fused", "party", "gram", "encode", "cot", "wire", "text", "probe"])
+    ap.add_argument("what", choices=["ti", "fused", "party", "gram", "encode", "cot", "wire", "text", "probe", "reduce"])
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=33)
     ap.add_argument("--cols", type=int, default=500)
@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--opt", action="append", default=[])
+    ap.add_argument("--devices", default="0,1", help="reduce: device list of the group")
     ap.add_argument("--novec", action="store_true", help="ti: values only (no mask vectors stored)")
     args = ap.parse_args()
 
@@ -120,6 +121,34 @@ def main():
         res.update(ms=ms, pairs=B, us_per_pair=ms * 1e3 / B, keystream_GBs=ks / ms / 1e6, aes_blocks_per_s=ks / 16 / (ms * 1e-3),
                    hbm_GBs_algorithmic=B * 4 * n * w / ms / 1e6, lds_bound_frac_at_1965MHz=(ks / 16 / (ms * 1e-3)) / (148 * 32 * 1.965e9 / 135))
         lib.p1_data_free(data)
+    elif args.what == "reduce":
+        # p1_group_reduce (the combination of the row shards' accumulators inside p1_group_finalize): peer reads by
+        # device 0 vs ncclAllReduce, for the accumulator of `cols` columns; wall clock per call including the sync,
+        # which is what a short step pays
+        import time
+        devs = [int(x) for x in args.devices.split(",")]
+        arr = (ctypes.c_int * len(devs))(*devs)
+        res["devices"] = devs
+        res["payload_bytes"] = int(lib.p1_acc_len(args.cols)) * 8
+        for mode, name in ((0, "p2p"), (1, "nccl")):
+            grp = c_vp()
+            lib.check(lib.p1_group_create(arr, len(devs), args.bits, bits2, ctypes.byref(grp)))
+            lib.check(lib.p1_group_set_option(grp, b"reduce", mode))
+            lib.check(lib.p1_group_acc_reset(grp, args.cols))
+            for _ in range(max(args.warmup, 3)):
+                lib.check(lib.p1_group_reduce(grp))
+            lib.check(lib.p1_group_sync(grp))
+            t0 = time.perf_counter()
+            for _ in range(args.reps):
+                lib.check(lib.p1_group_reduce(grp))
+                lib.check(lib.p1_group_sync(grp))
+            res[name + "_us_per_call_synced"] = (time.perf_counter() - t0) / args.reps * 1e6
+            t0 = time.perf_counter()
+            for _ in range(args.reps):
+                lib.check(lib.p1_group_reduce(grp))
+            lib.check(lib.p1_group_sync(grp))
+            res[name + "_us_per_call_back_to_back"] = (time.perf_counter() - t0) / args.reps * 1e6
+            lib.p1_group_destroy(grp)
     elif args.what == "probe":
         for ncols in (256, 192, 128, 64):
             tops, ms = ctypes.c_double(), ctypes.c_double()
