@@ -530,9 +530,14 @@ def main():
         try:   # DRAM bytes per launch of this kernel from the committed ncu --set full capture, if the shape matches
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 tr = json.load(f).get(dominant)
-            if tr and (tr.get("pairs") is None or (tr["pairs"] == batch and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"])):
+            if tr and tr.get("pairs") is None:
                 roofline["traffic"] = tr["bytes_per_launch"]
                 roofline["traffic_source"] = tr["source"]
+            elif tr and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"]:
+                # captured for tr["pairs"] pairs per launch; the traffic is linear in the pairs of a launch
+                per_launch = C / max(kd["launches_per_step"], 1)
+                roofline["traffic"] = tr["bytes_per_launch"] / tr["pairs"] * per_launch
+                roofline["traffic_source"] = tr["source"] + "; scaled from %d to the %.1f pairs of an average launch of this step" % (tr["pairs"], per_launch)
         except (OSError, ValueError, KeyError):
             pass
 

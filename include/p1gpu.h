@@ -96,8 +96,12 @@ const char *p1_kernel_class_name(int kernel_class);
  *                            and leaves it off (default 0).  Results are identical either way. */
 int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
 
+/* p1_dev_free / p1_host_free keep the block for the next request of the same size (up to 4 GB per device and
+ * 4 GB of page-locked memory per process): a party that serves run after run asks for the same buffers again.
+ * p1_pool_trim returns everything that is kept to the driver. */
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
 int p1_dev_free(p1_ctx *ctx, void *dev);
+void p1_pool_trim(void);
 int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes);
 /* page-locked host memory for buffers that cross PCIe every message (full-rate, truly asynchronous copies) */
 int p1_host_alloc(p1_ctx *ctx, size_t bytes, void **host);

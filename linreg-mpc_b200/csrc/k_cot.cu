@@ -15,6 +15,7 @@ struct p1_cot {
 	int device, bits;
 	int role;            // 0 receiver, 1 sender
 	uint32_t *keys_dev;  // [nk][44][128] round-key words, nk = 2 (receiver: k^0, k^1) or 1 (sender)
+	size_t keys_bytes;
 	uint32_t delta[4];
 	uint64_t pos, ot_base;
 	// receiver state between _extend and _finish
@@ -81,15 +82,26 @@ __device__ __forceinline__ void aes_ctr_block_r(const AesRegCtrKey &R, uint32_t 
 }
 
 // 32x32 bit-matrix transpose across a warp: lane r holds row r, returns row r of the transpose
-// (five butterfly steps: swap the off-diagonal j x j blocks of every 2j x 2j block)
+// (five butterfly steps: swap the off-diagonal j x j blocks of every 2j x 2j block).  Straight-line code:
+// the byte-granular steps (j = 16, 8) are one PRMT each; a bit-granular step takes the partner's word
+// rotated by j (lower lane of the pair) or 32 - j (upper lane) - the bits that wrap around land outside
+// the half that is kept - and one bit-select.
+template <int J>
+__device__ __forceinline__ uint32_t cot_bfly_bits(uint32_t x, bool up) {
+	constexpr uint32_t m = J == 4 ? 0x0f0f0f0fu : J == 2 ? 0x33333333u : 0x55555555u;
+	const uint32_t y = __shfl_xor_sync(0xffffffffu, x, J);
+	const uint32_t r = __funnelshift_l(y, y, up ? 32 - J : J);
+	const uint32_t keep = up ? ~m : m;
+	return (x & keep) | (r & ~keep);
+}
 __device__ __forceinline__ uint32_t cot_transpose32(uint32_t x, uint32_t lane) {
-#pragma unroll
-	for(int j = 16; j; j >>= 1) {
-		const uint32_t m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;
-		const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
-		x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y << j) & ~m));
-	}
-	return x;
+	uint32_t y = __shfl_xor_sync(0xffffffffu, x, 16);
+	x = __byte_perm(x, y, (lane & 16) ? 0x3276 : 0x5410);
+	y = __shfl_xor_sync(0xffffffffu, x, 8);
+	x = __byte_perm(x, y, (lane & 8) ? 0x3715 : 0x6240);
+	x = cot_bfly_bits<4>(x, lane & 4);
+	x = cot_bfly_bits<2>(x, lane & 2);
+	return cot_bfly_bits<1>(x, lane & 1);
 }
 
 // ROLE 0: receiver extend, ROLE 1: sender step.  TPI = tiles a 128-thread group works on per iteration
@@ -276,8 +288,9 @@ static int cot_new(p1_ctx *ctx, int role, const uint8_t (*seeds_a)[16], const ui
 	s->n_rows = 0;
 	memset(s->delta, 0, sizeof(s->delta));
 	if(delta) memcpy(s->delta, delta, 16); // little-endian words: bit i of Delta = bit (i%8) of byte i/8
-	cudaError_t e = cudaMalloc(&s->keys_dev, (size_t) nk * 44 * 128 * sizeof(uint32_t));
-	if(e == cudaSuccess) e = cudaMemcpy(s->keys_dev, h, (size_t) nk * 44 * 128 * sizeof(uint32_t), cudaMemcpyHostToDevice);
+	s->keys_bytes = (size_t) nk * 44 * 128 * sizeof(uint32_t);
+	s->keys_dev = (uint32_t *) p1_pool_dev_take(ctx->device, s->keys_bytes);
+	cudaError_t e = s->keys_dev ? cudaMemcpy(s->keys_dev, h, s->keys_bytes, cudaMemcpyHostToDevice) : cudaErrorMemoryAllocation;
 	free(h);
 	if(e != cudaSuccess) {
 		delete s;
@@ -303,8 +316,8 @@ extern "C" void p1_cot_free(p1_cot *s) {
 	if(!s) return;
 	cudaSetDevice(s->device);
 	cudaDeviceSynchronize();
-	cudaFree(s->keys_dev);
-	if(s->pads) cudaFree(s->pads);
+	p1_pool_dev_give(s->device, s->keys_dev, s->keys_bytes);
+	p1_pool_dev_give(s->device, s->pads, s->pads_bytes);
 	delete s;
 }
 
@@ -343,12 +356,12 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 		size_t need = P.tiles * 128 * (size_t) (s->bits / 8);
 		if(s->pads_bytes < need) {
 			if(s->pads) {
-				P1_CUDA(cudaStreamSynchronize(ctx->stream));
-				P1_CUDA(cudaFree(s->pads));
-				s->pads = NULL;
+				P1_CUDA(cudaDeviceSynchronize());
+				p1_pool_dev_give(s->device, s->pads, s->pads_bytes);
 				s->pads_bytes = 0;
 			}
-			P1_CUDA(cudaMalloc(&s->pads, need));
+			s->pads = p1_pool_dev_take(s->device, need);
+			P1_CHECK(s->pads, "p1_cot_receiver_extend: cannot allocate %zu bytes", need);
 			s->pads_bytes = need;
 		}
 		P.pads = s->pads;

@@ -351,12 +351,12 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 		const size_t need = (size_t) gs.m * ldp * L;
 		if(ctx->limb_ws_bytes < need) {
 			if(ctx->limb_ws) {
-				P1_CUDA(cudaStreamSynchronize(ctx->stream));
-				P1_CUDA(cudaFree(ctx->limb_ws));
-				ctx->limb_ws = NULL;
+				P1_CUDA(cudaDeviceSynchronize());
+				p1_pool_dev_give(ctx->device, ctx->limb_ws, ctx->limb_ws_bytes);
 				ctx->limb_ws_bytes = 0;
 			}
-			P1_CUDA(cudaMalloc(&ctx->limb_ws, need));
+			ctx->limb_ws = p1_pool_dev_take(ctx->device, need);
+			P1_CHECK(ctx->limb_ws, "p1_local_block: cannot allocate %zu bytes of digit planes", need);
 			ctx->limb_ws_bytes = need;
 		}
 		planes = (uint8_t *) ctx->limb_ws;

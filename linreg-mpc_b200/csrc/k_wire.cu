@@ -433,12 +433,12 @@ static int wire_ws(p1_ctx *ctx, size_t count, size_t tiles, uint32_t **sum, uint
 	const size_t need = p1_round_up(ent * 8, 256) + p1_round_up(ent * 4, 256);
 	if(ctx->wire_ws_bytes < need) {
 		if(ctx->wire_ws) {
-			P1_CUDA(cudaStreamSynchronize(ctx->stream));
-			P1_CUDA(cudaFree(ctx->wire_ws));
-			ctx->wire_ws = NULL;
+			P1_CUDA(cudaDeviceSynchronize());
+			p1_pool_dev_give(ctx->device, ctx->wire_ws, ctx->wire_ws_bytes);
 			ctx->wire_ws_bytes = 0;
 		}
-		P1_CUDA(cudaMalloc(&ctx->wire_ws, need));
+		ctx->wire_ws = p1_pool_dev_take(ctx->device, need);
+		P1_CHECK(ctx->wire_ws, "p1_msg: cannot allocate %zu bytes of workspace", need);
 		ctx->wire_ws_bytes = need;
 	}
 	*off = (uint64_t *) ctx->wire_ws;

@@ -4,6 +4,8 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <map>
+#include <unordered_map>
 
 static thread_local char g_err[512] = "";
 
@@ -45,6 +47,101 @@ int p1_small_to_dev(p1_ctx *ctx, const void *src, size_t bytes, size_t slot, con
 	return 0;
 }
 
+// Freed blocks are kept for the next request of the same size (device: per device; host: page-locked), up to
+// P1_POOL_MAX bytes each: a party that serves one run after another - and every test - asks for the same
+// buffers again, and cudaHostAlloc / cudaMalloc / cudaFree cost milliseconds per 100 MB and synchronise the device.
+#define P1_POOL_MAX ((size_t) 8 << 30)
+struct BlockPool {
+	std::mutex mu;
+	std::multimap<size_t, void *> blocks;
+	size_t held = 0;
+	void *take(size_t bytes) {
+		std::lock_guard<std::mutex> l(mu);
+		auto it = blocks.find(bytes);
+		if(it == blocks.end()) return NULL;
+		void *p = it->second;
+		blocks.erase(it);
+		held -= bytes;
+		return p;
+	}
+	bool give(size_t bytes, void *p) {
+		std::lock_guard<std::mutex> l(mu);
+		if(held + bytes > P1_POOL_MAX) return false;
+		blocks.emplace(bytes, p);
+		held += bytes;
+		return true;
+	}
+	template <typename F> void drain(F release) {
+		std::lock_guard<std::mutex> l(mu);
+		for(auto &b : blocks) release(b.second);
+		blocks.clear();
+		held = 0;
+	}
+};
+static BlockPool g_dev_pool[64], g_host_pool;
+static std::mutex g_size_mu;
+static std::unordered_map<const void *, size_t> g_block_size;   // bytes of every live p1_dev_alloc / p1_host_alloc block
+
+static void block_size_set(const void *p, size_t bytes) {
+	std::lock_guard<std::mutex> l(g_size_mu);
+	g_block_size[p] = bytes;
+}
+static size_t block_size_take(const void *p) {
+	std::lock_guard<std::mutex> l(g_size_mu);
+	auto it = g_block_size.find(p);
+	if(it == g_block_size.end()) return 0;
+	size_t b = it->second;
+	g_block_size.erase(it);
+	return b;
+}
+
+extern "C" void p1_pool_trim(void) {
+	int cur = 0;
+	cudaGetDevice(&cur);
+	for(int d = 0; d < 64; d++) {
+		bool any;
+		{
+			std::lock_guard<std::mutex> l(g_dev_pool[d].mu);
+			any = !g_dev_pool[d].blocks.empty();
+		}
+		if(!any) continue;
+		cudaSetDevice(d);
+		g_dev_pool[d].drain([](void *p) { cudaFree(p); });
+	}
+	cudaSetDevice(cur);
+	g_host_pool.drain([](void *p) { cudaFreeHost(p); });
+}
+
+void *p1_pool_dev_take(int device, size_t bytes) {
+	if(!bytes) bytes = 1;
+	void *p = g_dev_pool[device & 63].take(bytes);
+	if(p) return p;
+	if(cudaMalloc(&p, bytes) == cudaSuccess) return p;
+	cudaGetLastError();
+	p1_pool_trim();                     // the retired blocks may be what is in the way
+	if(cudaMalloc(&p, bytes) == cudaSuccess) return p;
+	cudaGetLastError();
+	return NULL;
+}
+void p1_pool_dev_give(int device, void *p, size_t bytes) {
+	if(!p) return;
+	if(!bytes) bytes = 1;
+	if(!g_dev_pool[device & 63].give(bytes, p)) cudaFree(p);
+}
+void *p1_pool_host_take(size_t bytes) {
+	if(!bytes) bytes = 1;
+	void *p = g_host_pool.take(bytes);
+	if(p) return p;
+	if(cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) return p;
+	cudaGetLastError();
+	return NULL;
+}
+void p1_pool_host_give(void *p, size_t bytes) {
+	if(!p) return;
+	if(!bytes) bytes = 1;
+	if(!g_host_pool.give(bytes, p)) cudaFreeHost(p);
+}
+
 extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_ctx **out) {
 	P1_CHECK(out, "p1_ctx_create: out may not be null");
 	*out = NULL;
@@ -58,6 +155,14 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	cudaDeviceProp prop;
 	P1_CUDA(cudaGetDeviceProperties(&prop, device));
 	P1_CHECK(prop.major == 10, "device %d is sm_%d%d; libp1gpu is built for sm_100a only", device, prop.major, prop.minor);
+	{
+		// temporaries come from the device's stream-ordered pool (p1_tmp): let it keep what it has handed out once
+		// instead of returning the memory to the driver at every synchronisation
+		cudaMemPool_t mp;
+		uint64_t keep = UINT64_MAX;
+		if(cudaDeviceGetDefaultMemPool(&mp, device) == cudaSuccess) cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &keep);
+		cudaGetLastError();
+	}
 	p1_ctx *ctx = new p1_ctx();
 	ctx->device = device;
 	ctx->bits_p1 = ring_bits_p1;
@@ -82,8 +187,8 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	for(int i = 0; i < P1_K_COUNT; i++) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
 	if(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
 	   cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming) != cudaSuccess ||
-	   cudaMallocHost(&ctx->pin, ctx->pin_bytes) != cudaSuccess ||
-	   cudaMalloc(&ctx->scratch, ctx->scratch_bytes) != cudaSuccess) {
+	   !(ctx->pin = p1_pool_host_take(ctx->pin_bytes)) ||
+	   !(ctx->scratch = p1_pool_dev_take(device, ctx->scratch_bytes))) {
 		delete ctx;
 		return p1_fail("p1_ctx_create: %s", cudaGetErrorString(cudaGetLastError()));
 	}
@@ -91,25 +196,22 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	return 0;
 }
 
-static void store_cache_drop(int device);
-
 extern "C" void p1_ctx_destroy(p1_ctx *ctx) {
 	if(!ctx) return;
 	cudaSetDevice(ctx->device);
-	cudaStreamSynchronize(ctx->stream);
-	store_cache_drop(ctx->device);
+	cudaDeviceSynchronize();
 	for(int i = 0; i < 2; i++) {
 		if(ctx->stage[i]) {
-			cudaFree(ctx->stage[i]);
+			p1_pool_dev_give(ctx->device, ctx->stage[i], ctx->stage_bytes);
 			cudaEventDestroy(ctx->stage_ev[i]);
 		}
 	}
-	if(ctx->limb_ws) cudaFree(ctx->limb_ws);
-	if(ctx->wire_ws) cudaFree(ctx->wire_ws);
+	p1_pool_dev_give(ctx->device, ctx->limb_ws, ctx->limb_ws_bytes);
+	p1_pool_dev_give(ctx->device, ctx->wire_ws, ctx->wire_ws_bytes);
 	for(auto &r : ctx->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
 	for(auto e : ctx->prof_pool) cudaEventDestroy(e);
-	cudaFree(ctx->scratch);
-	cudaFreeHost(ctx->pin);
+	p1_pool_dev_give(ctx->device, ctx->scratch, ctx->scratch_bytes);
+	p1_pool_host_give(ctx->pin, ctx->pin_bytes);
 	for(int i = 0; i < 8; i++) if(ctx->marks[i]) cudaEventDestroy(ctx->marks[i]);
 	cudaEventDestroy(ctx->ev);
 	cudaStreamDestroy(ctx->stream);
@@ -238,13 +340,20 @@ extern "C" int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev) {
 	P1_ENTER(ctx);
 	P1_CHECK(dev, "null output");
 	*dev = NULL;
-	P1_CUDA(cudaMalloc(dev, bytes ? bytes : 1));
+	if(!bytes) bytes = 1;
+	void *p = p1_pool_dev_take(ctx->device, bytes);
+	P1_CHECK(p, "p1_dev_alloc: cannot allocate %zu bytes on device %d", bytes, ctx->device);
+	block_size_set(p, bytes);
+	*dev = p;
 	return 0;
 }
 extern "C" int p1_dev_free(p1_ctx *ctx, void *dev) {
 	P1_ENTER(ctx);
-	P1_CUDA(cudaStreamSynchronize(ctx->stream));
-	P1_CUDA(cudaFree(dev));
+	if(!dev) return 0;
+	P1_CUDA(cudaDeviceSynchronize());           // as cudaFree would: no stream of the device still uses the block
+	const size_t bytes = block_size_take(dev);
+	if(bytes) p1_pool_dev_give(ctx->device, dev, bytes);
+	else P1_CUDA(cudaFree(dev));
 	return 0;
 }
 extern "C" int p1_dev_zero(p1_ctx *ctx, void *dev, size_t bytes) {
@@ -256,12 +365,19 @@ extern "C" int p1_host_alloc(p1_ctx *ctx, size_t bytes, void **host) {
 	P1_ENTER(ctx);
 	P1_CHECK(host, "p1_host_alloc: null output");
 	*host = NULL;
-	P1_CUDA(cudaHostAlloc(host, bytes ? bytes : 1, cudaHostAllocDefault));
+	if(!bytes) bytes = 1;
+	void *p = p1_pool_host_take(bytes);
+	P1_CHECK(p, "p1_host_alloc: cannot page-lock %zu bytes", bytes);
+	block_size_set(p, bytes);
+	*host = p;
 	return 0;
 }
 extern "C" int p1_host_free(p1_ctx *ctx, void *host) {
 	P1_ENTER(ctx);
-	if(host) P1_CUDA(cudaFreeHost(host));
+	if(!host) return 0;
+	const size_t bytes = block_size_take(host);
+	if(bytes) p1_pool_host_give(host, bytes);
+	else P1_CUDA(cudaFreeHost(host));
 	return 0;
 }
 extern "C" int p1_copy_h2d(p1_ctx *ctx, void *dst, const void *src, size_t bytes) {
@@ -283,13 +399,9 @@ extern "C" int p1_copy_d2h(p1_ctx *ctx, void *dst, const void *src, size_t bytes
 
 // ------------------------------------------------------------------ data
 
-// One retired column store per device is kept for the next p1_encode of the same size
-// (cudaMalloc/cudaFree of multi-GB buffers cost milliseconds and synchronise the device;
-// a provider re-encoding per run, and bench.py's step, hit this every time).
-struct StoreCache { void *xt; uint64_t *stats; size_t bytes, stat_bytes; uint8_t *planes; size_t plane_bytes; };
-static StoreCache g_store[64] = {};
-static std::mutex g_store_mu;
-
+// The column store comes from, and goes back to, the per-device block pool: a provider re-encoding per run, every
+// test and bench.py's first steps ask for the same multi-GB buffers again (cudaMalloc/cudaFree of those cost
+// milliseconds and synchronise the device).
 __global__ void k_zero_pads(unsigned char *__restrict__ xt, size_t col_bytes, size_t live_bytes, size_t cols) {
 	// zero bytes [live_bytes, col_bytes) of every column (rows >= n), 16 bytes per thread
 	const size_t pad = col_bytes - live_bytes, per = (pad + 15) / 16;
@@ -317,24 +429,7 @@ static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out
 	const size_t w = (size_t) (dt->bits / 8);
 	const size_t plane_bytes = (size_t) Lg * (d + 1) * dt->ld;
 	size_t bytes = (d + 1) * dt->ld * w, stat_bytes = (d + 1) * 4 * sizeof(uint64_t);
-	{
-		std::lock_guard<std::mutex> l(g_store_mu);
-		StoreCache &c = g_store[ctx->device & 63];
-		if(c.xt && c.bytes == bytes && c.stat_bytes == stat_bytes) {
-			dt->xt = c.xt;
-			dt->stats = c.stats;
-			c.xt = NULL;
-			c.stats = NULL;
-			if(c.planes && c.plane_bytes == plane_bytes) {
-				dt->planes = c.planes;
-				c.planes = NULL;
-			}
-		}
-	}
-	if(plane_bytes && !dt->planes && cudaMalloc(&dt->planes, plane_bytes) != cudaSuccess) {
-		cudaGetLastError();
-		dt->planes = NULL;                 // no room for the planes: the Gram falls back to k_limb_split
-	}
+	if(plane_bytes) dt->planes = (uint8_t *) p1_pool_dev_take(ctx->device, plane_bytes);   // no room for the planes: the Gram falls back to k_limb_split
 	if(dt->planes) {
 		dt->Lg = Lg;
 		dt->plane_bytes = plane_bytes;
@@ -343,11 +438,13 @@ static int data_alloc(p1_ctx *ctx, size_t n, size_t d, bool has_y, p1_data **out
 		const size_t kb0 = n / 128, per_kb = (size_t) Lg * (d + 1) * 128;
 		if(kb0 * 128 < dt->ld) cudaMemsetAsync(dt->planes + kb0 * per_kb, 0, (dt->ld / 128 - kb0) * per_kb, ctx->stream);
 	}
-	if(!dt->xt && (cudaMalloc(&dt->xt, bytes) != cudaSuccess || cudaMalloc(&dt->stats, stat_bytes) != cudaSuccess)) {
-		cudaError_t e = cudaGetLastError();
-		if(dt->xt) cudaFree(dt->xt);
+	dt->xt = p1_pool_dev_take(ctx->device, bytes);
+	dt->stats = dt->xt ? (uint64_t *) p1_pool_dev_take(ctx->device, stat_bytes) : NULL;
+	if(!dt->stats) {
+		p1_pool_dev_give(ctx->device, dt->xt, bytes);
+		p1_pool_dev_give(ctx->device, dt->planes, plane_bytes);
 		delete dt;
-		return p1_fail("p1_encode: cannot allocate %zu bytes on device: %s", bytes, cudaGetErrorString(e));
+		return p1_fail("p1_encode: cannot allocate %zu bytes on device %d", bytes, ctx->device);
 	}
 	dt->bytes = bytes;
 	dt->stat_bytes = stat_bytes;
@@ -366,38 +463,10 @@ extern "C" void p1_data_free(p1_data *dt) {
 	if(!dt) return;
 	cudaSetDevice(dt->device);
 	cudaDeviceSynchronize();
-	void *old_xt = NULL;
-	uint64_t *old_stats = NULL;
-	uint8_t *old_planes = NULL;
-	{
-		std::lock_guard<std::mutex> l(g_store_mu);
-		StoreCache &c = g_store[dt->device & 63];
-		old_xt = c.xt;
-		old_stats = c.stats;
-		old_planes = c.planes;
-		c.xt = dt->xt;
-		c.stats = dt->stats;
-		c.bytes = dt->bytes;
-		c.stat_bytes = dt->stat_bytes;
-		c.planes = dt->planes;
-		c.plane_bytes = dt->plane_bytes;
-	}
-	if(old_xt) cudaFree(old_xt);
-	if(old_stats) cudaFree(old_stats);
-	if(old_planes) cudaFree(old_planes);
+	p1_pool_dev_give(dt->device, dt->xt, dt->bytes);
+	p1_pool_dev_give(dt->device, dt->stats, dt->stat_bytes);
+	p1_pool_dev_give(dt->device, dt->planes, dt->plane_bytes);
 	delete dt;
-}
-
-// releases the retired column store of `device` (p1_ctx_destroy calls it)
-static void store_cache_drop(int device) {
-	std::lock_guard<std::mutex> l(g_store_mu);
-	StoreCache &c = g_store[device & 63];
-	if(c.xt) cudaFree(c.xt);
-	if(c.stats) cudaFree(c.stats);
-	if(c.planes) cudaFree(c.planes);
-	c.xt = NULL;
-	c.stats = NULL;
-	c.planes = NULL;
 }
 
 extern "C" size_t p1_data_rows(const p1_data *dt) { return dt ? dt->n : 0; }
@@ -412,13 +481,16 @@ static int ensure_stage(p1_ctx *ctx, size_t bytes) {
 	if(ctx->stage_bytes >= bytes) return 0;
 	for(int i = 0; i < 2; i++) {
 		if(ctx->stage[i]) {
-			P1_CUDA(cudaStreamSynchronize(ctx->stream));
-			P1_CUDA(cudaFree(ctx->stage[i]));
+			P1_CUDA(cudaDeviceSynchronize());
+			p1_pool_dev_give(ctx->device, ctx->stage[i], ctx->stage_bytes);
 		} else {
 			P1_CUDA(cudaEventCreateWithFlags(&ctx->stage_ev[i], cudaEventDisableTiming));
 		}
-		ctx->stage[i] = NULL;
-		P1_CUDA(cudaMalloc(&ctx->stage[i], bytes));
+		ctx->stage[i] = p1_pool_dev_take(ctx->device, bytes);
+		if(!ctx->stage[i]) {
+			ctx->stage_bytes = 0;
+			return p1_fail("p1_encode: cannot allocate a %zu-byte staging buffer", bytes);
+		}
 	}
 	ctx->stage_bytes = bytes;
 	return 0;

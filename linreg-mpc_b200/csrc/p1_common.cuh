@@ -45,6 +45,14 @@ struct p1_ctx {
 	uint64_t prof_n[P1_K_COUNT];
 };
 
+// retired blocks kept per device / for page-locked host memory (p1_api.cu).  take: NULL if the driver has no
+// memory left even after the kept blocks were released; give: the caller guarantees nothing on the device still
+// uses the block (it synchronised, as a cudaFree would have)
+void *p1_pool_dev_take(int device, size_t bytes);
+void p1_pool_dev_give(int device, void *p, size_t bytes);
+void *p1_pool_host_take(size_t bytes);
+void p1_pool_host_give(void *p, size_t bytes);
+
 // call right before a kernel launch; P1_LAUNCHED closes the bracket
 void p1_prof_begin(p1_ctx *ctx, int cls);
 void p1_prof_end(p1_ctx *ctx);

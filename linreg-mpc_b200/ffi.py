@@ -80,6 +80,7 @@ SIGNATURES = {
     "p1_finalize": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_i, c_i, c_d, c_vp, c_vp,
                           ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
     "p1_finalize_async": (c_i, [c_vp, c_vp, c_sz, c_sz, c_vp, c_i, c_i, c_d, c_vp, c_vp, c_vp]),
+    "p1_pool_trim": (None, []),
     "p1_encode_again": (c_i, [c_vp, c_vp, c_vp, c_vp, c_d, c_i]),
     "p1_group_create": (c_i, [c_vp, c_i, c_i, c_i, ctypes.POINTER(c_vp)]),
     "p1_group_destroy": (None, [c_vp]),

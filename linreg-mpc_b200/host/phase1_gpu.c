@@ -306,6 +306,73 @@ static int next_run(pair_cursor *pc, const config *c, size_t batch, pair_run *r)
 
 /* ------------------------------------------------------------------ trusted initializer */
 
+/* A second sending thread: the TI's messages to party A and to party B of a run travel on different connections,
+ * so the two streams go out side by side (each connection still carries its messages in the reference's order;
+ * only the interleaving ACROSS connections, which no peer can observe, differs from :281-284). */
+typedef struct {
+	pthread_t th;
+	pthread_mutex_t mu;
+	pthread_cond_t cv;
+	int started, state;            /* 0 idle, 1 job posted, 2 quit */
+	ProtocolDesc *pd;
+	const uint8_t *base;
+	const uint64_t *sizes;
+	size_t count, stride;
+	int status;
+} wire_sender;
+
+static void *wire_sender_main(void *arg) {
+	wire_sender *w = arg;
+	pthread_mutex_lock(&w->mu);
+	for(;;) {
+		while(w->state == 0) pthread_cond_wait(&w->cv, &w->mu);
+		if(w->state == 2) break;
+		pthread_mutex_unlock(&w->mu);
+		int st = 0;
+		for(size_t p = 0; p < w->count && !st; p++) st = send_wire(w->pd, w->base + p * w->stride, w->sizes[p]);
+		pthread_mutex_lock(&w->mu);
+		w->status = st;
+		w->state = 0;
+		pthread_cond_broadcast(&w->cv);
+	}
+	pthread_mutex_unlock(&w->mu);
+	return NULL;
+}
+static int wire_sender_start(wire_sender *w) {
+	memset(w, 0, sizeof(*w));
+	pthread_mutex_init(&w->mu, NULL);
+	pthread_cond_init(&w->cv, NULL);
+	if(pthread_create(&w->th, NULL, wire_sender_main, w)) return 1;
+	w->started = 1;
+	return 0;
+}
+static void wire_sender_post(wire_sender *w, ProtocolDesc *pd, const uint8_t *base, const uint64_t *sizes, size_t count, size_t stride) {
+	pthread_mutex_lock(&w->mu);
+	w->pd = pd; w->base = base; w->sizes = sizes; w->count = count; w->stride = stride;
+	w->state = 1;
+	pthread_cond_broadcast(&w->cv);
+	pthread_mutex_unlock(&w->mu);
+}
+static int wire_sender_wait(wire_sender *w) {
+	pthread_mutex_lock(&w->mu);
+	while(w->state == 1) pthread_cond_wait(&w->cv, &w->mu);
+	const int st = w->status;
+	pthread_mutex_unlock(&w->mu);
+	return st;
+}
+static void wire_sender_stop(wire_sender *w) {
+	if(!w->started) return;
+	pthread_mutex_lock(&w->mu);
+	while(w->state == 1) pthread_cond_wait(&w->cv, &w->mu);
+	w->state = 2;
+	pthread_cond_broadcast(&w->cv);
+	pthread_mutex_unlock(&w->mu);
+	pthread_join(w->th, NULL);
+	pthread_mutex_destroy(&w->mu);
+	pthread_cond_destroy(&w->cv);
+	w->started = 0;
+}
+
 /* everything of one run up to the host copy of its 2 x count messages, asynchronously, into wire half `set`:
  * x, y, r, <x,y> (:270-274), xy - r and r (:277-278), msg_a = {y, xy - r} (class 0), msg_b = {x, r} (class 1) */
 static int ti_prepare(gpu_state *g, const uint8_t key[16], const config *c, const pair_run *r, int set, uint64_t *xy_dev, uint64_t *r_dev) {
@@ -334,7 +401,10 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 	if(use_ot) return 0;                 /* the TI takes no part in the OT variant (:256) */
 	double t_wait = 0, t_send = 0;
 	const double t_begin = now_s();
+	wire_sender to_b;
+	memset(&to_b, 0, sizeof(to_b));
 	check(!gpu_init(&g, c->n, 2, 2), "could not set up the GPU");
+	check(!wire_sender_start(&to_b), "could not start the second sending thread");
 	uint8_t key[16];
 	check(!p1host_ti_key(key), "could not draw the PRG key");
 	GCHECK(p1_dev_alloc(g.ctx, g.batch * 8, (void **) &xy_dev));
@@ -355,12 +425,14 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 		t0 = now_s();
 		const uint64_t *sa = sizes_host_at(&g, set, 0), *sb = sizes_host_at(&g, set, 1);
 		const uint8_t *wa = wire_host_at(&g, set, 0), *wb = wire_host_at(&g, set, 1);
-		for(size_t p = 0; p < cur.count; p++) {          /* the reference's order on the wire: a, b per pair (:281-284) */
+		wire_sender_post(&to_b, self->peer[cur.owner_j], wb, sb, cur.count, g.stride);
+		for(size_t p = 0; p < cur.count; p++) {
 			status = send_wire(self->peer[cur.owner_i], wa + p * g.stride, sa[p]);
-			check(!status, "Could not send message to party A (%d)", cur.owner_i);
-			status = send_wire(self->peer[cur.owner_j], wb + p * g.stride, sb[p]);
-			check(!status, "Could not send message to party B (%d)", cur.owner_j);
+			if(status) break;
 		}
+		const int status_b = wire_sender_wait(&to_b);     /* also: the buffers of this half are free again */
+		check(!status, "Could not send message to party A (%d)", cur.owner_i);
+		check(!status_b, "Could not send message to party B (%d)", cur.owner_j);
 		status = 1;
 		t_send += now_s() - t0;
 		cur = nxt;
@@ -370,6 +442,7 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 	if(trace_on()) fprintf(stderr, "p1gpu trace TI: waiting for the GPU %.3f  sending %.3f  total %.3f s, batch %zu\n", t_wait, t_send, now_s() - t_begin, g.batch);
 	status = 0;
 error:
+	wire_sender_stop(&to_b);
 	if(g.ctx) {
 		p1_group_sync(g.grp);
 		if(xy_dev) p1_dev_free(g.ctx, xy_dev);
@@ -398,8 +471,7 @@ static int load_inputs(gpu_state *g, config *c, int precision, p1_gdata **data) 
 	const long end = ftell(c->input);
 	check(end >= pos && fseek(c->input, pos, SEEK_SET) == 0, "fseek: %s", strerror(errno));
 	const size_t bytes = (size_t) (end - pos);
-	text = malloc(bytes + 1);
-	check(text, "Out of memory");
+	GCHECK(p1_host_alloc(ctx, bytes + 1, (void **) &text));      /* page-locked: the copy to the GPU runs at link rate */
 	check(fread(text, 1, bytes, c->input) == bytes, "fread: %s", strerror(errno));
 	text[bytes] = 0;
 	const size_t n = c->n, d = c->d, need = 2 + n * d + 1 + n;
@@ -449,7 +521,7 @@ static int load_inputs(gpu_state *g, config *c, int precision, p1_gdata **data) 
 error:
 	if(tok_dev) p1_dev_free(ctx, tok_dev);
 	free(deferred);
-	free(text);
+	if(text) p1_host_free(ctx, text);
 	return status;
 }
 

@@ -135,19 +135,24 @@ def main():
             lib.check(lib.p1_group_create(arr, len(devs), args.bits, bits2, ctypes.byref(grp)))
             lib.check(lib.p1_group_set_option(grp, b"reduce", mode))
             lib.check(lib.p1_group_acc_reset(grp, args.cols))
-            for _ in range(max(args.warmup, 3)):
-                lib.check(lib.p1_group_reduce(grp))
-            lib.check(lib.p1_group_sync(grp))
-            t0 = time.perf_counter()
-            for _ in range(args.reps):
-                lib.check(lib.p1_group_reduce(grp))
+            # p1_group_reduce is a no-op on accumulators that are already combined: every repetition zeroes them
+            # again (p1_group_acc_reset), and the cost of that alone is measured and subtracted
+            def loop(reduce, synced):
+                t0 = time.perf_counter()
+                for _ in range(args.reps):
+                    lib.check(lib.p1_group_acc_reset(grp, args.cols))
+                    if reduce:
+                        lib.check(lib.p1_group_reduce(grp))
+                    if synced:
+                        lib.check(lib.p1_group_sync(grp))
                 lib.check(lib.p1_group_sync(grp))
-            res[name + "_us_per_call_synced"] = (time.perf_counter() - t0) / args.reps * 1e6
-            t0 = time.perf_counter()
-            for _ in range(args.reps):
-                lib.check(lib.p1_group_reduce(grp))
-            lib.check(lib.p1_group_sync(grp))
-            res[name + "_us_per_call_back_to_back"] = (time.perf_counter() - t0) / args.reps * 1e6
+                return (time.perf_counter() - t0) / args.reps * 1e6
+            for _ in range(3):
+                loop(True, True)
+            base_s, base_b = loop(False, True), loop(False, False)
+            res[name + "_us_per_call_synced"] = loop(True, True) - base_s
+            res[name + "_us_per_call_back_to_back"] = loop(True, False) - base_b
+            res[name + "_reset_only_us"] = {"synced": base_s, "back_to_back": base_b}
             lib.p1_group_destroy(grp)
     elif args.what == "probe":
         for ncols in (256, 192, 128, 64):
