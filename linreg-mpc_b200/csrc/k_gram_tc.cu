@@ -259,6 +259,135 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 	}
 }
 
+// ------------------------------------------------------------------ one-digit blocks of up to 256 columns
+//
+// A block whose words fit ONE digit (|word| <= 127: the 32-bit configurations, where a value is ~10 units of the
+// scale) and that has at most 256 columns is multiplied whole by every CTA: a pipeline stage is the block's
+// 128 rows x cols digit tile, loaded ONCE, and serves as both operands - B = all columns (N = cols), A = its
+// first / second 128 columns (two MMAs per K-step into TMEM columns [0,128) and [128,384)).  The tiled kernel
+// above moves every digit through L2 once per 128 x 64 tile that touches it (6 tiles at 201 columns: 5.7x the
+// bytes of the planes, which capped it at 25 % tensor-pipe activity); here every digit crosses L2 -> SM once and
+// the kernel runs at the rate HBM delivers the planes.  One s32 chunk holds 131071 rows, so a CTA's row slice is
+// normally a single chunk: the epilogue adds TMEM straight into the packed share (red.global.add.u64).
+struct TsParams {
+	TcSet gs;
+	int stages;
+	uint32_t stage_bytes;  // cols * 128
+	int n0, n1;            // N of the two MMAs (0: no second row tile)
+	int nblk, blk_per_cta, chunk_blks;
+	uint64_t *acc;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1) k_gram_whole(const __grid_constant__ CUtensorMap map, const TsParams P) {
+	extern __shared__ __align__(1024) uint8_t smem_raw[];
+	__shared__ __align__(8) uint64_t bar_full[8], bar_empty[8], bar_tfull, bar_tempty;
+	__shared__ uint32_t tmem_base_s;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int S = P.stages;
+	uint8_t *smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+	const int blk_lo = (int) blockIdx.x * P.blk_per_cta;
+	const int blk_hi = blk_lo + P.blk_per_cta < P.nblk ? blk_lo + P.blk_per_cta : P.nblk;
+	const int nb = blk_hi - blk_lo;          // > 0 by construction of the grid
+	if(threadIdx.x == 0) {
+		for(int s = 0; s < S; s++) {
+			mbar_init(&bar_full[s], 1);
+			mbar_init(&bar_empty[s], 1);
+		}
+		mbar_init(&bar_tfull, 1);
+		mbar_init(&bar_tempty, 128);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+		asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map)) : "memory");
+	}
+	if(warp == 1) {
+		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u) : "memory");
+		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+	}
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t tmem = tmem_base_s;
+
+	if(warp == 0) {
+		if(lane == 0) {
+			int s = 0;
+			uint32_t ph = 0;
+			for(int b = 0; b < nb; b++) {
+				mbar_wait(&bar_empty[s], ph ^ 1u);
+				mbar_expect_tx(&bar_full[s], P.stage_bytes);
+				tma_load_4d(smem + (size_t) s * P.stage_bytes, &map, &bar_full[s], 0, 0, 0, blk_lo + b);
+				if(++s == S) { s = 0; ph ^= 1u; }
+			}
+		}
+	} else if(warp == 1) {
+		if(lane == 0) {
+			const uint32_t lo0 = ((smem_u32(smem) >> 4) & 0x3fffu) | (1u << 16);
+			const uint32_t id0 = tc_idesc(P.n0), id1 = tc_idesc(P.n1 ? P.n1 : 16);
+			int s = 0, in_chunk = 0;
+			uint32_t ph = 0, chunk = 0;
+			for(int b = 0; b < nb; b++) {
+				if(in_chunk == 0) {
+					mbar_wait(&bar_tempty, chunk & 1u);     // the epilogue has read the previous chunk out of TMEM
+					tc_fence_after();
+				}
+				mbar_wait(&bar_full[s], ph);
+				tc_fence_after();
+				const uint32_t t_lo = lo0 + (uint32_t) s * (P.stage_bytes >> 4);
+#pragma unroll
+				for(int k4 = 0; k4 < TC_BK / 32; k4++) {
+					const uint32_t keep = (in_chunk | k4) ? 1u : 0u;  // the first K-step of a chunk overwrites the accumulators
+					const uint64_t db = tc_desc(t_lo + (uint32_t) (k4 * 2));
+					tc_mma_i8(tmem, db, db, id0, keep);
+					if(P.n1) tc_mma_i8(tmem + 128u, tc_desc(t_lo + (uint32_t) ((TC_BM * TC_BK >> 4) + k4 * 2)), db, id1, keep);
+				}
+				tc_commit(&bar_empty[s]);
+				if(++s == S) { s = 0; ph ^= 1u; }
+				if(++in_chunk == P.chunk_blks || b + 1 == nb) {
+					tc_commit(&bar_tfull);
+					chunk++;
+					in_chunk = 0;
+				}
+			}
+		}
+	} else {
+		// epilogue: warp q owns TMEM lanes [32q, 32q+32) = output rows 32q+lane (and 128+32q+lane)
+		const int q = warp & 3;
+		const uint32_t tlane = tmem + ((uint32_t) (32 * q) << 16);
+		mbar_arrive(&bar_tempty);
+		const int nchunks = (nb + P.chunk_blks - 1) / P.chunk_blks;
+		for(int ch = 0; ch < nchunks; ch++) {
+			mbar_wait(&bar_tfull, (uint32_t) ch & 1u);
+			tc_fence_after();
+			for(int ta = 0; ta < (P.n1 ? 2 : 1); ta++) {
+				const int a = TC_BM * ta + 32 * q + lane;
+				const int ncol = ta ? P.n1 : P.n0;
+				// columns b < a only: groups past the warp's last row are all upper triangle
+				const int gmax = (TC_BM * ta + 32 * q + 31) / 32;
+				for(int g = 0; g <= gmax && 32 * g < ncol; g++) {
+					uint32_t v[32];
+					tmem_ld32(tlane + (uint32_t) (128 * ta + 32 * g), v);
+					if(a < P.gs.m) {
+#pragma unroll
+						for(int c = 0; c < 32; c++) {
+							const int b = 32 * g + c;
+							if(b < a && b < P.gs.mc && v[c]) p1_red_add(P.acc + tc_slot(P.gs, a, b), (uint64_t) (int64_t) (int32_t) v[c]);
+						}
+					}
+				}
+			}
+			if(ch + 1 < nchunks) {
+				tc_fence_before();
+				mbar_arrive(&bar_tempty);
+			}
+		}
+	}
+	tc_fence_before();
+	__syncthreads();
+	if(warp == 1) {
+		tc_fence_after();
+		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+	}
+}
+
 typedef void (*tc_kernel_t)(const CUtensorMap, const CUtensorMap, const TcParams);
 template <int WD> static tc_kernel_t tc_kernel_for(int L) {
 	switch(L) {
@@ -383,6 +512,38 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 	CUresult r2 = encode(&mapB, dt, 4, planes, gdim, gstr, boxB, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 		CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	P1_CHECK(r1 == CUDA_SUCCESS && r2 == CUDA_SUCCESS, "p1_local_block: cuTensorMapEncodeTiled failed (%d, %d)", (int) r1, (int) r2);
+
+	if(L == 1 && gs.m <= 256 && ctx->opt_tc_whole) {
+		// one-digit block of at most 256 columns: every CTA multiplies the whole block over its slice of the rows
+		const int cols = (gs.m + 15) / 16 * 16;
+		CUtensorMap map;
+		cuuint32_t box[4] = {(cuuint32_t) (TC_BK / esz), (cuuint32_t) cols, 1, 1};
+		CUresult r = encode(&map, dt, 4, planes, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+			CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+		P1_CHECK(r == CUDA_SUCCESS, "p1_local_block: cuTensorMapEncodeTiled failed (%d)", (int) r);
+		TsParams Q;
+		Q.gs = gs;
+		Q.stage_bytes = (uint32_t) cols * TC_BK;
+		Q.n0 = cols < TC_BM ? cols : TC_BM;
+		Q.n1 = cols > TC_BM ? cols : 0;
+		int stages = (int) ((size_t) 216 * 1024 / Q.stage_bytes);
+		Q.stages = stages > 8 ? 8 : stages;
+		Q.nblk = (int) ((data->n + TC_BK - 1) / TC_BK);
+		Q.chunk_blks = 131071 / TC_BK;
+		if(ctx->opt_tc_chunk_blocks > 0 && ctx->opt_tc_chunk_blocks < Q.chunk_blks) Q.chunk_blks = (int) ctx->opt_tc_chunk_blocks;
+		int ctas = ctx->sm_count;
+		if(ctx->opt_tc_max_slices > 0 && ctas > ctx->opt_tc_max_slices) ctas = (int) ctx->opt_tc_max_slices;
+		if(ctas > Q.nblk) ctas = Q.nblk;
+		Q.blk_per_cta = (Q.nblk + ctas - 1) / ctas;
+		ctas = (Q.nblk + Q.blk_per_cta - 1) / Q.blk_per_cta;
+		Q.acc = acc_dev;
+		const size_t smem = (size_t) Q.stages * Q.stage_bytes + 1024;
+		P1_CUDA(cudaFuncSetAttribute(k_gram_whole, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		p1_prof_begin(ctx, P1_K_GRAM_TC);
+		k_gram_whole<<<(unsigned) ctas, TC_THREADS, smem, ctx->stream>>>(map, Q);
+		P1_LAUNCHED(ctx);
+		return 0;
+	}
 
 	TcParams P;
 	P.gs = gs;

@@ -192,6 +192,35 @@ def test_local_block_tcgen05_shapes(p1lib, oracle, b1, b2, prec, prec2):
     p1lib.p1_ctx_destroy(ctx)
 
 
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("d,owns", [(16, False), (100, True), (128, False), (128, True), (200, True), (255, True), (256, False)])
+def test_local_block_tcgen05_one_digit_whole_block(p1lib, oracle, bits, d, owns):
+    """one-digit words (|word| <= 127: what the 32-bit configurations hold) in a block of at most 256 columns
+    take the kernel in which every CTA multiplies the WHOLE block over its rows (k_gram_whole: one tile load per
+    K-block, two MMAs into 384 TMEM columns, straight red.add epilogue).  Against the oracle, for one and two row
+    tiles, ragged rows, with the row slices and the s32 chunks forced small, and against the tiled kernel."""
+    rng = np.random.default_rng(7 * d + bits)
+    n = 3001
+    Xw = _signed_words(rng, n, d, bits, 7)
+    yw = _signed_words(rng, n, 1, bits, 7)[:, 0].copy()
+    Xw[2, d - 1] = 127                                                   # the largest one-digit magnitude
+    ctx = mkctx(p1lib, bits, bits)
+    data = from_words(p1lib, ctx, Xw, yw)
+    L = ctypes.c_int(0)
+    p1lib.check(p1lib.p1_gram_digits(ctx, data, 0, d, int(owns), ctypes.byref(L)))
+    assert L.value == 1
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, owns, bits, 2)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_max_slices", 3))
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_chunk_blocks", 3))   # 8 K-blocks per CTA -> 3 chunks
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, owns, bits, 2)
+    if d > 40:
+        _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 5, d - 3, False, bits, 2)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_whole", 0))
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, owns, bits, 2)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 def _limb_split_launches(p1lib, ctx):
     from linreg_mpc_b200 import ffi
     ms, cnt = ctypes.c_double(), ctypes.c_uint64()
