@@ -272,9 +272,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const __grid_constant
 struct TsParams {
 	TcSet gs;
 	int stages;
-	uint32_t stage_bytes;  // cols * 128
+	uint32_t blk_bytes;    // cols * 128: one K-block of the block's digit tile
+	int kpb;               // K-blocks per pipeline stage (narrow blocks: several, so that a stage is worth a TMA)
 	int n0, n1;            // N of the two MMAs (0: no second row tile)
-	int nblk, blk_per_cta, chunk_blks;
+	int nblk, blk_per_cta, chunk_blks;   // in stages (groups of kpb K-blocks)
 	uint64_t *acc;
 };
 
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_whole(const __grid_const
 	const int blk_lo = (int) blockIdx.x * P.blk_per_cta;
 	const int blk_hi = blk_lo + P.blk_per_cta < P.nblk ? blk_lo + P.blk_per_cta : P.nblk;
 	const int nb = blk_hi - blk_lo;          // > 0 by construction of the grid
+	const uint32_t stage_bytes = P.blk_bytes * (uint32_t) P.kpb;
 	if(threadIdx.x == 0) {
 		for(int s = 0; s < S; s++) {
 			mbar_init(&bar_full[s], 1);
@@ -313,8 +315,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_whole(const __grid_const
 			uint32_t ph = 0;
 			for(int b = 0; b < nb; b++) {
 				mbar_wait(&bar_empty[s], ph ^ 1u);
-				mbar_expect_tx(&bar_full[s], P.stage_bytes);
-				tma_load_4d(smem + (size_t) s * P.stage_bytes, &map, &bar_full[s], 0, 0, 0, blk_lo + b);
+				mbar_expect_tx(&bar_full[s], stage_bytes);
+				tma_load_4d(smem + (size_t) s * stage_bytes, &map, &bar_full[s], 0, 0, 0, (blk_lo + b) * P.kpb);
 				if(++s == S) { s = 0; ph ^= 1u; }
 			}
 		}
@@ -331,13 +333,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_whole(const __grid_const
 				}
 				mbar_wait(&bar_full[s], ph);
 				tc_fence_after();
-				const uint32_t t_lo = lo0 + (uint32_t) s * (P.stage_bytes >> 4);
+				uint32_t t_lo = lo0 + (uint32_t) s * (stage_bytes >> 4);
+				for(int kb = 0; kb < P.kpb; kb++, t_lo += P.blk_bytes >> 4) {
 #pragma unroll
-				for(int k4 = 0; k4 < TC_BK / 32; k4++) {
-					const uint32_t keep = (in_chunk | k4) ? 1u : 0u;  // the first K-step of a chunk overwrites the accumulators
-					const uint64_t db = tc_desc(t_lo + (uint32_t) (k4 * 2));
-					tc_mma_i8(tmem, db, db, id0, keep);
-					if(P.n1) tc_mma_i8(tmem + 128u, tc_desc(t_lo + (uint32_t) ((TC_BM * TC_BK >> 4) + k4 * 2)), db, id1, keep);
+					for(int k4 = 0; k4 < TC_BK / 32; k4++) {
+						const uint32_t keep = (in_chunk | kb | k4) ? 1u : 0u;  // the first K-step of a chunk overwrites the accumulators
+						const uint64_t db = tc_desc(t_lo + (uint32_t) (k4 * 2));
+						tc_mma_i8(tmem, db, db, id0, keep);
+						if(P.n1) tc_mma_i8(tmem + 128u, tc_desc(t_lo + (uint32_t) ((TC_BM * TC_BK >> 4) + k4 * 2)), db, id1, keep);
+					}
 				}
 				tc_commit(&bar_empty[s]);
 				if(++s == S) { s = 0; ph ^= 1u; }
@@ -518,18 +522,31 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 		const int cols = (gs.m + 15) / 16 * 16;
 		CUtensorMap map;
 		cuuint32_t box[4] = {(cuuint32_t) (TC_BK / esz), (cuuint32_t) cols, 1, 1};
+		TsParams Q;
+		Q.gs = gs;
+		Q.blk_bytes = (uint32_t) cols * TC_BK;
+		// narrow blocks: several K-blocks per stage (one TMA box of up to 24 KB)
+		Q.kpb = (int) ((size_t) 24576 / Q.blk_bytes);
+		if(Q.kpb < 1) Q.kpb = 1;
+		if(Q.kpb > 8) Q.kpb = 8;
+		const int nblk = (int) ((data->n + TC_BK - 1) / TC_BK);
+		while(Q.kpb > 1 && (nblk + Q.kpb - 1) / Q.kpb < ctx->sm_count) Q.kpb--;     // few rows: rather one stage per SM
+		box[3] = (cuuint32_t) Q.kpb;
 		CUresult r = encode(&map, dt, 4, planes, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 			CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 		P1_CHECK(r == CUDA_SUCCESS, "p1_local_block: cuTensorMapEncodeTiled failed (%d)", (int) r);
-		TsParams Q;
-		Q.gs = gs;
-		Q.stage_bytes = (uint32_t) cols * TC_BK;
+		const size_t stage_bytes = (size_t) Q.blk_bytes * Q.kpb;
 		Q.n0 = cols < TC_BM ? cols : TC_BM;
 		Q.n1 = cols > TC_BM ? cols : 0;
-		int stages = (int) ((size_t) 216 * 1024 / Q.stage_bytes);
+		// an A operand is always 128 rows: when the block has fewer than 128 (256) columns the last rows of the
+		// (second) row tile lie past the K-block, for the last K-block of the last stage past the stage (their
+		// products land in output rows >= m, which nobody reads) - the allocation covers them
+		const size_t a_end = (size_t) (Q.n1 ? 2 : 1) * TC_BM * TC_BK;
+		const size_t overrun = a_end > Q.blk_bytes ? a_end - Q.blk_bytes : 0;
+		int stages = (int) (((size_t) 216 * 1024 - overrun) / stage_bytes);
 		Q.stages = stages > 8 ? 8 : stages;
-		Q.nblk = (int) ((data->n + TC_BK - 1) / TC_BK);
-		Q.chunk_blks = 131071 / TC_BK;
+		Q.nblk = (nblk + Q.kpb - 1) / Q.kpb;
+		Q.chunk_blks = 131071 / (TC_BK * Q.kpb);
 		if(ctx->opt_tc_chunk_blocks > 0 && ctx->opt_tc_chunk_blocks < Q.chunk_blks) Q.chunk_blks = (int) ctx->opt_tc_chunk_blocks;
 		int ctas = ctx->sm_count;
 		if(ctx->opt_tc_max_slices > 0 && ctas > ctx->opt_tc_max_slices) ctas = (int) ctx->opt_tc_max_slices;
@@ -537,7 +554,7 @@ int p1_launch_gram_tc(p1_ctx *ctx, const p1_data *data, size_t col_lo, size_t co
 		Q.blk_per_cta = (Q.nblk + ctas - 1) / ctas;
 		ctas = (Q.nblk + Q.blk_per_cta - 1) / Q.blk_per_cta;
 		Q.acc = acc_dev;
-		const size_t smem = (size_t) Q.stages * Q.stage_bytes + 1024;
+		const size_t smem = (size_t) Q.stages * stage_bytes + overrun + 1024;
 		P1_CUDA(cudaFuncSetAttribute(k_gram_whole, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 		p1_prof_begin(ctx, P1_K_GRAM_TC);
 		k_gram_whole<<<(unsigned) ctas, TC_THREADS, smem, ctx->stream>>>(map, Q);

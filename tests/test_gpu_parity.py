@@ -221,6 +221,23 @@ def test_local_block_tcgen05_one_digit_whole_block(p1lib, oracle, bits, d, owns)
     p1lib.p1_ctx_destroy(ctx)
 
 
+@pytest.mark.parametrize("bits,d", [(32, 40), (64, 20), (32, 90)])
+def test_local_block_tcgen05_whole_block_narrow_many_rows(p1lib, oracle, bits, d):
+    """narrow one-digit blocks over enough rows that a pipeline stage of k_gram_whole holds several K-blocks
+    (one TMA box of up to 24 KB; the last stage of the last CTA runs past the rows and is zero-filled)"""
+    rng = np.random.default_rng(11 * d + bits)
+    n = 148 * 128 * 5 + 777
+    Xw = _signed_words(rng, n, d, bits, 7)
+    yw = _signed_words(rng, n, 1, bits, 7)[:, 0].copy()
+    ctx = mkctx(p1lib, bits, bits)
+    data = from_words(p1lib, ctx, Xw, yw)
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 0, d, True, bits, 2)
+    p1lib.check(p1lib.p1_ctx_set_option(ctx, b"gram_tc_chunk_blocks", 2))
+    _check_local_block(p1lib, oracle, ctx, data, Xw, yw, 1, d - 2, False, bits, 2)
+    p1lib.p1_data_free(data)
+    p1lib.p1_ctx_destroy(ctx)
+
+
 def _limb_split_launches(p1lib, ctx):
     from linreg_mpc_b200 import ffi
     ms, cnt = ctypes.c_double(), ctypes.c_uint64()
