@@ -161,8 +161,8 @@ __device__ __forceinline__ void fu_full(FuPair<W> &S, int64_t o, const uint32_t 
 	}
 }
 
-template <typename W, bool ALIGNED>
-__global__ void __launch_bounds__(FU_THREADS, 1) k_masking_fused(const FusedParams P) {
+template <typename W, bool ALIGNED, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams P) {
 	extern __shared__ __align__(256) uint8_t smem[];
 	constexpr int w = sizeof(W);
 	uint8_t *sT = smem + aes_table_offset(smem, 0, 0);
@@ -273,22 +273,30 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_masking_fused(const FusedPara
 	}
 }
 
-template <typename W>
-static int launch_fused(p1_ctx *ctx, const FusedParams &P, bool aligned) {
+template <typename W, bool ALIGNED, int THREADS>
+static int launch_fused_t(p1_ctx *ctx, const FusedParams &P) {
 	const size_t smem = AES_SMEM_BYTES;
-	if(aligned) P1_CUDA(cudaFuncSetAttribute(k_masking_fused<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-	else P1_CUDA(cudaFuncSetAttribute(k_masking_fused<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	P1_CUDA(cudaFuncSetAttribute(k_masking_fused<W, ALIGNED, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	const uint64_t units = (uint64_t) P.count * P.units_per_pair;
 	P1_CHECK(units < 0xffffffffull, "p1_masking_fused: batch too large (%llu work units)", (unsigned long long) units);
-	const unsigned threads = ctx->opt_fused_threads ? (unsigned) ctx->opt_fused_threads : FU_THREADS;
 	uint64_t grid = (uint64_t) ctx->sm_count;
-	const uint64_t need = (units + threads / 32 - 1) / (threads / 32);
+	const uint64_t need = (units + THREADS / 32 - 1) / (THREADS / 32);
 	if(grid > need) grid = need;
 	p1_prof_begin(ctx, P1_K_MASKING_FUSED);
-	if(aligned) k_masking_fused<W, true><<<(unsigned) grid, threads, smem, ctx->stream>>>(P);
-	else k_masking_fused<W, false><<<(unsigned) grid, threads, smem, ctx->stream>>>(P);
+	k_masking_fused<W, ALIGNED, THREADS><<<(unsigned) grid, THREADS, smem, ctx->stream>>>(P);
 	P1_LAUNCHED(ctx);
 	return 0;
+}
+
+// CTA size: 512 threads by default; option "fused_threads" picks one of the other compiled sizes (each with the
+// register budget of its own launch bound)
+template <typename W>
+static int launch_fused(p1_ctx *ctx, const FusedParams &P, bool aligned) {
+	const long t = ctx->opt_fused_threads ? ctx->opt_fused_threads : FU_THREADS;
+#define FU_CASE(T) if(t == T) return aligned ? launch_fused_t<W, true, T>(ctx, P) : launch_fused_t<W, false, T>(ctx, P);
+	FU_CASE(384) FU_CASE(512) FU_CASE(640) FU_CASE(768) FU_CASE(1024)
+#undef FU_CASE
+	P1_CHECK(0, "p1_masking_fused: no kernel for %ld threads per CTA (384, 512, 640, 768, 1024)", t);
 }
 
 extern "C" int p1_masking_fused(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total, size_t row0,

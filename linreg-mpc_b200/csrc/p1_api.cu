@@ -267,7 +267,7 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 		ctx->opt_ti_threads = value;
 	}
 	else if(!strcmp(name, "fused_threads")) {
-		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "fused_threads must be a multiple of 32 in [32,512]");
+		P1_CHECK(value == 0 || value == 384 || value == 512 || value == 640 || value == 768 || value == 1024, "fused_threads must be 0 (default), 384, 512, 640, 768 or 1024");
 		ctx->opt_fused_threads = value;
 	}
 	else if(!strcmp(name, "encode_planes")) ctx->opt_encode_planes = value;
