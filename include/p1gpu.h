@@ -204,6 +204,14 @@ int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count
                    size_t n_total, size_t row0, size_t n_rows,
                    void *x_dev, void *y_dev, size_t ld_words,
                    uint64_t *xy_dev, uint64_t *r_dev);
+/* The same with one key per word class: x = S_kx[W0 + k], y = S_ky[W0 + n + k], r = S_kr[W0 + 2n] (same positions,
+ * three keystreams).  This is what seed-instead-of-vector TI messages need (host/phase1_gpu.c with
+ * P1GPU_SEEDED_MASKS=1): party b shares kx with the TI and expands x itself, party a shares ky and expands y, so
+ * neither learns the other's mask; a key may be NULL when its words are not requested.  With kx = ky = kr this is
+ * p1_ti_generate. */
+int p1_ti_generate_keys(p1_ctx *ctx, const uint8_t key_x[16], const uint8_t key_y[16], const uint8_t key_r[16],
+                        uint64_t q0, size_t count, size_t n_total, size_t row0, size_t n_rows,
+                        void *x_dev, void *y_dev, size_t ld_words, uint64_t *xy_dev, uint64_t *r_dev);
 /* value_a[p] = xy[p] - r[p], value_b[p] = r[p] (src/phase1.c:277-278), after xy was all-reduced */
 int p1_ti_values(p1_ctx *ctx, const uint64_t *xy_dev, const uint64_t *r_dev, size_t count,
                  uint64_t *value_a_dev, uint64_t *value_b_dev);
@@ -445,6 +453,8 @@ int p1_gvec_scatter(p1_group *grp, const void *full_dev0, size_t ld0, size_t cou
  * values live on device 0; cols / slots: host or device-0... host arrays (each context stages its copy) */
 int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total,
                          p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0);
+int p1_group_ti_generate_keys(p1_group *grp, const uint8_t key_x[16], const uint8_t key_y[16], const uint8_t key_r[16],
+                              uint64_t q0, size_t count, size_t n_total, p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0);
 int p1_group_party_b_mask(p1_group *grp, const p1_gdata *data, const int32_t *cols, size_t count, const p1_gvec *T, p1_gvec *out);
 int p1_group_party_a_step(p1_group *grp, const p1_gdata *data, const int32_t *cols, const int64_t *slots, size_t count,
                           const p1_gvec *T, const p1_gvec *in, p1_gvec *out);

@@ -112,7 +112,7 @@ int aes_device_T0(p1_ctx *ctx, const uint32_t **dT0) {
 #define TI_THREADS_DEFAULT 512  // leaves registers and thread slots on every SM for the HBM-bound party kernels of the other pipe
 
 struct TiParams {
-	AesCtrKey key;
+	AesCtrKey kx, ky, kr;   // keys of the x, y and r words (one key three times in the reference's stream, p1_ti_generate)
 	uint64_t q0;
 	uint32_t count;
 	uint64_t n_total, row0, n_rows;
@@ -193,16 +193,16 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 			const bool full = __all_sync(0xffffffffu, o >= 0 && o + 16 <= (int64_t) nbytes);
 			if(o <= -16 || o >= (int64_t) nbytes) continue;      // before the start / past the end
 			uint32_t xs[4] = {0, 0, 0, 0}, ys[4] = {0, 0, 0, 0};
-			if(need_x) aes_ctr_block_g(P.key, lb, B, gx, xs);
+			if(need_x) aes_ctr_block_g(P.kx, lb, B, gx, xs);
 			if(need_y) {
 				const uint64_t By = ((B << 4) + ydelta) >> 4;
 				if(ALIGNED) {
-					aes_ctr_block_g(P.key, lb, By, gy, ys);
+					aes_ctr_block_g(P.ky, lb, By, gy, ys);
 				} else {
 					// y bytes for these positions straddle two stream blocks
 					uint32_t ya[4], yb[4];
-					aes_ctr_block_g(P.key, lb, By, gy, ya);
-					aes_ctr_block_g(P.key, lb, By + 1, gy1, yb);
+					aes_ctr_block_g(P.ky, lb, By, gy, ya);
+					aes_ctr_block_g(P.ky, lb, By + 1, gy1, yb);
 					const uint32_t ws = ysh >> 2; // whole 32-bit words (ysh is a multiple of w >= 4)
 #pragma unroll
 					for(int c = 0; c < 4; c++) {
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(TI_THREADS, 1) k_ti_generate(const TiParams P)
 			// r = S[W0 + 2 n_total] (src/phase1.c:273)
 			const uint64_t Rb = (W0 + 2 * P.n_total) * w;
 			uint32_t rs[4];
-			aes_ctr_block(P.key, lb, Rb >> 4, rs);
+			aes_ctr_block(P.kr, lb, Rb >> 4, rs);
 			const uint32_t wi = (uint32_t) (Rb & 15) >> 2;
 			uint32_t lo = 0, hi = 0;
 #pragma unroll
@@ -286,14 +286,15 @@ static int launch_ti(p1_ctx *ctx, const TiParams &P, bool aligned) {
 	return 0;
 }
 
-extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count,
-	size_t n_total, size_t row0, size_t n_rows, void *x_dev, void *y_dev, size_t ld_words,
+extern "C" int p1_ti_generate_keys(p1_ctx *ctx, const uint8_t key_x[16], const uint8_t key_y[16], const uint8_t key_r[16],
+	uint64_t q0, size_t count, size_t n_total, size_t row0, size_t n_rows, void *x_dev, void *y_dev, size_t ld_words,
 	uint64_t *xy_dev, uint64_t *r_dev) {
 	P1_CHECK(ctx, "null context");
 	std::lock_guard<std::mutex> lock_(ctx->mu);
 	P1_CUDA(cudaSetDevice(ctx->device));
 	if(!count) return 0;
-	P1_CHECK(key, "p1_ti_generate: null key");
+	const bool need_x = x_dev || xy_dev, need_y = y_dev || xy_dev;
+	P1_CHECK((!need_x || key_x) && (!need_y || key_y) && (!r_dev || key_r), "p1_ti_generate: null key for a requested output");
 	P1_CHECK(n_rows > 0 && row0 + n_rows <= n_total, "p1_ti_generate: rows [%zu,%zu) outside [0,%zu)", row0, row0 + n_rows, n_total);
 	P1_CHECK((!x_dev && !y_dev) || ld_words >= n_rows, "p1_ti_generate: ld_words %zu < n_rows %zu", ld_words, n_rows);
 	P1_CHECK(count <= 0xffffffffu, "p1_ti_generate: batch too large");
@@ -301,7 +302,13 @@ extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, s
 	TiParams P;
 	if(aes_device_T0(ctx, &P.T0)) return 1;
 	// most of a launch shares the high counter word of its first stream block
-	aes_host_ctr_key(key, (uint32_t) ((((uint64_t) q0 * (2 * (uint64_t) n_total + 1) + row0) * w) >> 36), &P.key);
+	const uint32_t hi = (uint32_t) ((((uint64_t) q0 * (2 * (uint64_t) n_total + 1) + row0) * w) >> 36);
+	static const uint8_t zero_key[16] = {0};
+	aes_host_ctr_key(key_x ? key_x : zero_key, hi, &P.kx);
+	if(key_y == key_x || (key_x && key_y && !memcmp(key_x, key_y, 16))) P.ky = P.kx;
+	else aes_host_ctr_key(key_y ? key_y : zero_key, hi, &P.ky);
+	if(key_r == key_x || (key_x && key_r && !memcmp(key_x, key_r, 16))) P.kr = P.kx;
+	else aes_host_ctr_key(key_r ? key_r : zero_key, hi, &P.kr);
 	P.q0 = q0;
 	P.count = (uint32_t) count;
 	P.n_total = n_total;
@@ -320,4 +327,12 @@ extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, s
 	bool aligned = ((uint64_t) n_total * w) % 16 == 0;
 	if(w == 8) return launch_ti<uint64_t>(ctx, P, aligned);
 	return launch_ti<uint32_t>(ctx, P, aligned);
+}
+
+extern "C" int p1_ti_generate(p1_ctx *ctx, const uint8_t key[16], uint64_t q0, size_t count,
+	size_t n_total, size_t row0, size_t n_rows, void *x_dev, void *y_dev, size_t ld_words,
+	uint64_t *xy_dev, uint64_t *r_dev) {
+	P1_CHECK(ctx, "null context");
+	P1_CHECK(key || !count, "p1_ti_generate: null key");
+	return p1_ti_generate_keys(ctx, key, key, key, q0, count, n_total, row0, n_rows, x_dev, y_dev, ld_words, xy_dev, r_dev);
 }

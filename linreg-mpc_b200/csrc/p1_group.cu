@@ -68,11 +68,13 @@ struct p1_gcot {
 // ------------------------------------------------------------------ helpers
 
 static void group_rows(int ndev, size_t n_total, int g, size_t *row0, size_t *rows) {
-	size_t per = (n_total + ndev - 1) / ndev;
-	per = p1_round_up(per, 256);
-	size_t r0 = (size_t) g * per;
+	// whole 256-row blocks, spread evenly (the first blocks % ndev devices hold one more): nobody is empty once
+	// there are at least ndev blocks
+	const size_t blocks = (n_total + 255) / 256, q = blocks / ndev, r = blocks % ndev;
+	size_t r0 = ((size_t) g * q + ((size_t) g < r ? (size_t) g : r)) * 256;
+	size_t r1 = r0 + (q + ((size_t) g < r ? 1 : 0)) * 256;
 	if(r0 > n_total) r0 = n_total;
-	size_t r1 = r0 + per < n_total ? r0 + per : n_total;
+	if(r1 > n_total) r1 = n_total;
 	*row0 = r0;
 	*rows = r1 - r0;
 }
@@ -445,9 +447,9 @@ extern "C" int p1_gvec_scatter(p1_group *grp, const void *full_dev0, size_t ld0,
 
 // ------------------------------------------------------------------ masking protocol, fanned out
 
-extern "C" int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total,
-	p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0) {
-	P1_CHECK(grp && key, "p1_group_ti_generate: invalid arguments");
+extern "C" int p1_group_ti_generate_keys(p1_group *grp, const uint8_t key_x[16], const uint8_t key_y[16], const uint8_t key_r[16],
+	uint64_t q0, size_t count, size_t n_total, p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0) {
+	P1_CHECK(grp, "p1_group_ti_generate: invalid arguments");
 	P1_CHECK((!x || (x->grp == grp && x->n_total == n_total && count <= x->batch)) && (!y || (y->grp == grp && y->n_total == n_total && count <= y->batch)),
 		"p1_group_ti_generate: vectors do not match the call");
 	if(!count) return 0;
@@ -461,7 +463,7 @@ extern "C" int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64
 			return 0;
 		}
 		uint64_t *xy = !xy_dev0 ? NULL : (g == 0 ? xy_dev0 : grp->part[g]);
-		return p1_ti_generate(grp->ctx[g], key, q0, count, n_total, row0, rows, x ? x->buf[g] : NULL, y ? y->buf[g] : NULL,
+		return p1_ti_generate_keys(grp->ctx[g], key_x, key_y, key_r, q0, count, n_total, row0, rows, x ? x->buf[g] : NULL, y ? y->buf[g] : NULL,
 			x ? x->ld[g] : (y ? y->ld[g] : rows), xy, g == 0 ? r_dev0 : NULL);
 	});
 	if(st || group_join(grp)) return 1;
@@ -471,6 +473,12 @@ extern "C" int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64
 		return reduce_p2p(grp, bufs, count);
 	}
 	return 0;
+}
+
+extern "C" int p1_group_ti_generate(p1_group *grp, const uint8_t key[16], uint64_t q0, size_t count, size_t n_total,
+	p1_gvec *x, p1_gvec *y, uint64_t *xy_dev0, uint64_t *r_dev0) {
+	P1_CHECK(grp && key, "p1_group_ti_generate: invalid arguments");
+	return p1_group_ti_generate_keys(grp, key, key, key, q0, count, n_total, x, y, xy_dev0, r_dev0);
 }
 
 static int check_party(p1_group *grp, const p1_gdata *gd, const p1_gvec *a, const p1_gvec *b, const p1_gvec *c, size_t count) {

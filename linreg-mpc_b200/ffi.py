@@ -59,6 +59,7 @@ SIGNATURES = {
     "p1_gram_digits": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, ctypes.POINTER(c_i)]),
     "p1_diag_sequential": (c_i, [c_vp, c_vp, c_sz, c_sz, c_i, c_vp]),
     "p1_ti_generate": (c_i, [c_vp, c_cp, c_u64, c_sz, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
+    "p1_ti_generate_keys": (c_i, [c_vp, c_cp, c_cp, c_cp, c_u64, c_sz, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "p1_ti_values": (c_i, [c_vp, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "p1_party_b_mask": (c_i, [c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz]),
     "p1_party_a_step": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz, c_vp]),
@@ -103,6 +104,7 @@ SIGNATURES = {
     "p1_gvec_gather": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz]),
     "p1_gvec_scatter": (c_i, [c_vp, c_vp, c_sz, c_sz, c_vp]),
     "p1_group_ti_generate": (c_i, [c_vp, c_cp, c_u64, c_sz, c_sz, c_vp, c_vp, c_vp, c_vp]),
+    "p1_group_ti_generate_keys": (c_i, [c_vp, c_cp, c_cp, c_cp, c_u64, c_sz, c_sz, c_vp, c_vp, c_vp, c_vp]),
     "p1_group_party_b_mask": (c_i, [c_vp, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "p1_group_party_a_step": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_vp, c_vp]),
     "p1_group_party_b_share": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),

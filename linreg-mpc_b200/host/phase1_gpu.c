@@ -39,6 +39,15 @@
  * reads message p+1 from its socket while message p travels to the device, and brings a batch of
  * serialised messages back with one asynchronous copy.
  *
+ * Seeded masks (P1GPU_SEEDED_MASKS=1 in the environment of the TI and of every provider; default off =
+ * the reference's byte stream).  The TI derives one key per provider, K_p = SHA-256(label || K || p)[0..16), and sends
+ * it to provider p once.  For cross pair q the masks keep their positions in the stream of p1gpu.h (x = S[W0 + k],
+ * y = S[W0 + n + k], r = S[W0 + 2n]) but x is read from the keystream of K_b (b = owner of row j), y from that of K_a
+ * and r from the TI's own K (p1_ti_generate_keys): party a expands y, party b expands x on its own GPUs, neither can
+ * expand the other's mask, and the TI's message of :277-284 shrinks to {vector = (empty), value}: the same proto2
+ * message with no vector field, 2-11 bytes instead of ~9.5 n.  Message count and order on every socket are the
+ * reference's; the party <-> party messages are unchanged.
+ *
  * Two things the reference obtains inside Obliv-C are hooks here (weak defaults below):
  *   p1host_ti_key   : the TI's PRG key (newBCipherRandomGen draws a random one, :243)
  *   p1host_base_ot  : the kappa = 128 base OTs of honestOTExt{Sender,Recver}New (:394,397)
@@ -103,6 +112,52 @@ static double now_s(void) {
 static int trace_on(void) {
 	const char *e = getenv("P1GPU_TRACE");
 	return e && atoi(e) > 0;
+}
+
+/* ------------------------------------------------------------------ seeded masks (see the header) */
+
+void p1host_sha256(const uint8_t *msg, size_t len, uint8_t out[32]);     /* host/base_ot.c */
+
+static int seeded_masks(void) {
+	const char *e = getenv("P1GPU_SEEDED_MASKS");
+	return e && atoi(e) > 0;
+}
+
+/* K_p = SHA-256("linreg-mpc p1gpu seeded mask key" || K || LE32(p))[0..16), p = 0-based node index */
+static void seeded_party_key(const uint8_t ti_key[16], int party, uint8_t out[16]) {
+	static const char label[32] = "linreg-mpc p1gpu seeded mask key";
+	uint8_t msg[32 + 16 + 4], dig[32];
+	memcpy(msg, label, 32);
+	memcpy(msg + 32, ti_key, 16);
+	for(int k = 0; k < 4; k++) msg[48 + k] = (uint8_t) ((uint32_t) party >> (8 * k));
+	p1host_sha256(msg, sizeof(msg), dig);
+	memcpy(out, dig, 16);
+}
+
+/* SecureMultiplication.Msg with an empty vector: field 2 (value), wire type 0 */
+static size_t value_msg_encode(uint64_t value, uint8_t out[16]) {
+	size_t k = 0;
+	out[k++] = 0x10;
+	do {
+		uint8_t b = (uint8_t) (value & 0x7f);
+		value >>= 7;
+		out[k++] = (uint8_t) (b | (value ? 0x80 : 0));
+	} while(value);
+	return k;
+}
+static int value_msg_decode(const uint8_t *in, size_t size, uint64_t *value) {
+	if(size < 2 || in[0] != 0x10) return 1;
+	uint64_t v = 0;
+	size_t k = 1;
+	for(int shift = 0; k < size && shift < 64; shift += 7) {
+		const uint8_t b = in[k++];
+		v |= (uint64_t) (b & 0x7f) << shift;
+		if(!(b & 0x80)) {
+			*value = v;
+			return k == size ? 0 : 1;
+		}
+	}
+	return 1;
 }
 
 static int owner_of(size_t row, const config *c) {
@@ -196,7 +251,11 @@ static int gpu_init(gpu_state *g, size_t n, int nvec, int sets) {
 		GCHECK(p1_dev_alloc(g->ctx, g->batch * g->ld * sizeof(ufixed_p1_t), &g->vec[k]));
 		if(ndev > 1) GCHECK(p1_gvec_alloc(g->grp, n, g->batch, &g->gv[k]));
 	}
-	if(sets) {
+	if(sets < 0) {            /* the TI with seeded masks: values only */
+		g->sets = 0;
+		GCHECK(p1_dev_alloc(g->ctx, g->batch * 8, (void **) &g->vals_dev));
+		GCHECK(p1_dev_alloc(g->ctx, g->batch * 8, (void **) &g->vals2_dev));
+	} else if(sets) {
 		const size_t msgs = (size_t) sets * 2 * g->batch;
 		GCHECK(p1_dev_alloc(g->ctx, msgs * g->stride, (void **) &g->wire_dev));
 		GCHECK(p1_dev_alloc(g->ctx, msgs * 8, (void **) &g->sizes_dev));
@@ -248,17 +307,18 @@ error:
 }
 
 /* party kernels on the party's data: one device directly, several through the row slices */
-static int do_b_mask(gpu_state *g, const p1_gdata *gd, const int32_t *cols, size_t count) {      /* vec[2] = col + vec[0] */
+/* t_sliced: the TI vector is already in the row slices gv[0] (seeded masks are expanded there) */
+static int do_b_mask(gpu_state *g, const p1_gdata *gd, const int32_t *cols, size_t count, int t_sliced) {      /* vec[2] = col + vec[0] */
 	if(g->ndev == 1) return p1_party_b_mask(g->ctx, p1_gdata_shard(gd, 0), cols, count, g->vec[0], g->ld, g->vec[2], g->ld);
-	if(p1_gvec_scatter(g->grp, g->vec[0], g->ld, count, g->gv[0])) return 1;
+	if(!t_sliced && p1_gvec_scatter(g->grp, g->vec[0], g->ld, count, g->gv[0])) return 1;
 	if(p1_group_party_b_mask(g->grp, gd, cols, count, g->gv[0], g->gv[2])) return 1;
 	return p1_gvec_gather(g->grp, g->gv[2], count, g->vec[2], g->ld);
 }
-static int do_a_step(gpu_state *g, const p1_gdata *gd, const int32_t *cols, const int64_t *slots, size_t count) {
+static int do_a_step(gpu_state *g, const p1_gdata *gd, const int32_t *cols, const int64_t *slots, size_t count, int t_sliced) {
 	/* vec[2] = col - vec[0]; share += <vec[1], vec[0]> */
 	if(g->ndev == 1) return p1_party_a_step(g->ctx, p1_gdata_shard(gd, 0), cols, slots, count, g->vec[0], g->ld, g->vec[1], g->ld,
 		g->vec[2], g->ld, p1_group_acc_dev(g->grp, 0));
-	if(p1_gvec_scatter(g->grp, g->vec[0], g->ld, count, g->gv[0])) return 1;
+	if(!t_sliced && p1_gvec_scatter(g->grp, g->vec[0], g->ld, count, g->gv[0])) return 1;
 	if(p1_gvec_scatter(g->grp, g->vec[1], g->ld, count, g->gv[1])) return 1;
 	if(p1_group_party_a_step(g->grp, gd, cols, slots, count, g->gv[0], g->gv[1], g->gv[2])) return 1;
 	return p1_gvec_gather(g->grp, g->gv[2], count, g->vec[2], g->ld);
@@ -392,6 +452,28 @@ error:
 	return 1;
 }
 
+/* seeded masks: only <x,y> and r are computed (x under the key of b = owner_j, y under that of a = owner_i, r under
+ * the TI's own key); the two values of every pair go to the host half `set` of vals_host */
+static int ti_prepare_seeded(gpu_state *g, const uint8_t key[16], const config *c, const pair_run *r, int set,
+	uint64_t *xy_dev, uint64_t *r_dev, uint64_t *vals_host) {
+	uint8_t ka[16], kb[16];
+	seeded_party_key(key, r->owner_i, ka);
+	seeded_party_key(key, r->owner_j, kb);
+	if(g->ndev == 1) {
+		GCHECK(p1_ti_generate_keys(g->ctx, kb, ka, key, r->q0, r->count, c->n, 0, c->n, NULL, NULL, g->ld, xy_dev, r_dev));
+	} else {
+		GCHECK(p1_group_ti_generate_keys(g->grp, kb, ka, key, r->q0, r->count, c->n, NULL, NULL, xy_dev, r_dev));
+	}
+	GCHECK(p1_ti_values(g->ctx, xy_dev, r_dev, r->count, g->vals_dev, g->vals2_dev));
+	uint64_t *vh = vals_host + (size_t) set * 2 * g->batch;
+	GCHECK(p1_copy_d2h_async(g->ctx, vh, g->vals_dev, r->count * 8));
+	GCHECK(p1_copy_d2h_async(g->ctx, vh + g->batch, g->vals2_dev, r->count * 8));
+	GCHECK(wire_mark(g, set));
+	return 0;
+error:
+	return 1;
+}
+
 int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 	(void) precision;
 	gpu_state g;
@@ -403,26 +485,54 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 	const double t_begin = now_s();
 	wire_sender to_b;
 	memset(&to_b, 0, sizeof(to_b));
-	check(!gpu_init(&g, c->n, 2, 2), "could not set up the GPU");
+	const int seeded = seeded_masks();
+	uint64_t *vals_host = NULL;
+	check(!gpu_init(&g, c->n, seeded ? 0 : 2, seeded ? -1 : 2), "could not set up the GPU");
 	check(!wire_sender_start(&to_b), "could not start the second sending thread");
 	uint8_t key[16];
 	check(!p1host_ti_key(key), "could not draw the PRG key");
 	GCHECK(p1_dev_alloc(g.ctx, g.batch * 8, (void **) &xy_dev));
 	GCHECK(p1_dev_alloc(g.ctx, g.batch * 8, (void **) &r_dev));
+	if(seeded) {
+		GCHECK(p1_host_alloc(g.ctx, (size_t) 2 * 2 * g.batch * 8, (void **) &vals_host));
+		for(int p = 2; p < self->num_parties; p++) {          /* every provider's mask key, once */
+			uint8_t kp[16];
+			seeded_party_key(key, p, kp);
+			check(!send_wire(self->peer[p], kp, sizeof(kp)), "Could not send the mask key to party %d", p + 1);
+		}
+	}
 
 	pair_cursor pc = {0, 0, 0};
 	pair_run cur, nxt;
 	int have = next_run(&pc, c, g.batch, &cur), set = 0;
-	if(have) check(!ti_prepare(&g, key, c, &cur, set, xy_dev, r_dev), "could not prepare the first run");
+	if(have) check(!(seeded ? ti_prepare_seeded(&g, key, c, &cur, set, xy_dev, r_dev, vals_host) : ti_prepare(&g, key, c, &cur, set, xy_dev, r_dev)),
+		"could not prepare the first run");
 	while(have) {
 		check(cur.owner_i >= 2 && cur.owner_j >= 2, "Invalid owners %d, %d for rows %zd, %zd", cur.owner_i, cur.owner_j, cur.i, cur.j0);
 		/* the GPU works on the next run while this one goes out on the sockets */
 		const int have_next = next_run(&pc, c, g.batch, &nxt);
-		if(have_next) check(!ti_prepare(&g, key, c, &nxt, set ^ 1, xy_dev, r_dev), "could not prepare a run");
+		if(have_next) check(!(seeded ? ti_prepare_seeded(&g, key, c, &nxt, set ^ 1, xy_dev, r_dev, vals_host) : ti_prepare(&g, key, c, &nxt, set ^ 1, xy_dev, r_dev)),
+			"could not prepare a run");
 		double t0 = now_s();
 		GCHECK(wire_ready(&g, set));
 		t_wait += now_s() - t0;
 		t0 = now_s();
+		if(seeded) {
+			/* {vector = (empty), value}: a first, then b, per pair (:281-284) */
+			const uint64_t *va = vals_host + (size_t) set * 2 * g.batch, *vb = va + g.batch;
+			for(size_t p = 0; p < cur.count; p++) {
+				uint8_t m[16];
+				size_t len = value_msg_encode(va[p], m);
+				check(!send_wire(self->peer[cur.owner_i], m, len), "Could not send message to party A (%d)", cur.owner_i);
+				len = value_msg_encode(vb[p], m);
+				check(!send_wire(self->peer[cur.owner_j], m, len), "Could not send message to party B (%d)", cur.owner_j);
+			}
+			t_send += now_s() - t0;
+			cur = nxt;
+			have = have_next;
+			set ^= 1;
+			continue;
+		}
 		const uint64_t *sa = sizes_host_at(&g, set, 0), *sb = sizes_host_at(&g, set, 1);
 		const uint8_t *wa = wire_host_at(&g, set, 0), *wb = wire_host_at(&g, set, 1);
 		wire_sender_post(&to_b, self->peer[cur.owner_j], wb, sb, cur.count, g.stride);
@@ -447,6 +557,7 @@ error:
 		p1_group_sync(g.grp);
 		if(xy_dev) p1_dev_free(g.ctx, xy_dev);
 		if(r_dev) p1_dev_free(g.ctx, r_dev);
+		if(vals_host) p1_host_free(g.ctx, vals_host);
 	}
 	gpu_free(&g);
 	return status;
@@ -629,6 +740,9 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 	uint64_t *acc_host = NULL;
 	int32_t *cols = NULL;
 	int64_t *slots = NULL;
+	uint64_t *vals_host = NULL;
+	uint8_t my_key[16];
+	const int seeded = !use_ot && seeded_masks();
 	int status = 1;
 	if(res_A) *res_A = NULL;
 	if(res_b) *res_b = NULL;
@@ -681,6 +795,11 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 		check(!bad, "an OT thread failed");
 	} else {
 		GCHECK(p1_group_acc_reset(g.grp, d));
+		if(seeded) {
+			size_t size = 0;
+			check(!recv_wire(self->peer[0], my_key, sizeof(my_key), &size) && size == sizeof(my_key), "Could not receive the mask key from the TI");
+			GCHECK(p1_host_alloc(g.ctx, g.batch * 8, (void **) &vals_host));
+		}
 		/* pairs we own both rows of, and the diagonal statistics (:562-571) */
 		GCHECK(p1_group_local_block(g.grp, data, lo, hi, me == P - 1, P1_GRAM_AUTO));
 		cols = malloc(g.batch * sizeof(*cols));
@@ -700,7 +819,24 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 			}
 			/* random vectors and values from the TI (:170) */
 			double t0 = now_s(), t1;
-			check(!recv_to_device(&g, self->peer[0], count, g.vec[0], g.vals_dev), "Could not receive message from TI");
+			if(seeded) {
+				/* the values arrive, the vector is expanded here: y (party a) or x (party b) of the run's pairs under our key */
+				for(size_t p = 0; p < count; p++) {
+					uint8_t m[16];
+					size_t size = 0;
+					check(!recv_wire(self->peer[0], m, sizeof(m), &size), "Could not receive message from TI");
+					check(!value_msg_decode(m, size, &vals_host[p]), "msg__unpack: malformed value message from the TI");
+				}
+				GCHECK(p1_copy_h2d(g.ctx, g.vals_dev, vals_host, count * 8));
+				const uint8_t *kx = r.owner_i == me ? NULL : my_key, *ky = r.owner_i == me ? my_key : NULL;
+				if(g.ndev == 1) {
+					GCHECK(p1_ti_generate_keys(g.ctx, kx, ky, NULL, r.q0, count, c->n, 0, c->n, kx ? g.vec[0] : NULL, ky ? g.vec[0] : NULL, g.ld, NULL, NULL));
+				} else {
+					GCHECK(p1_group_ti_generate_keys(g.grp, kx, ky, NULL, r.q0, count, c->n, kx ? g.gv[0] : NULL, ky ? g.gv[0] : NULL, NULL, NULL));
+				}
+			} else {
+				check(!recv_to_device(&g, self->peer[0], count, g.vec[0], g.vals_dev), "Could not receive message from TI");
+			}
 			t_ti += (t1 = now_s()) - t0;
 			if(r.owner_i == me) {                                  /* party a (:173-196) */
 				ProtocolDesc *pb = self->peer[r.owner_j];
@@ -710,7 +846,7 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 				check(!status, "Could not receive message from party B (%d)", r.owner_j);
 				status = 1;
 				t_peer += (t0 = now_s()) - t1;
-				GCHECK(do_a_step(&g, data, cols, slots, count));           /* out = a - y, share += <b + x, y> */
+				GCHECK(do_a_step(&g, data, cols, slots, count, seeded));           /* out = a - y, share += <b + x, y> */
 				check(!pack_start(&g, 0, 1, g.vec[2], g.zero_dev, count), "could not serialise the messages for party B");
 				GCHECK(wire_mark(&g, 0));
 				GCHECK(wire_ready(&g, 0));
@@ -720,7 +856,7 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 				t_send += now_s() - t1;
 			} else {                                             /* party b (:198-224) */
 				ProtocolDesc *pa = self->peer[r.owner_i];
-				GCHECK(do_b_mask(&g, data, cols, count));                  /* out = b + x */
+				GCHECK(do_b_mask(&g, data, cols, count, seeded));                  /* out = b + x */
 				check(!pack_start(&g, 0, 1, g.vec[2], g.zero_dev, count), "could not serialise the messages for party A");
 				GCHECK(wire_mark(&g, 0));
 				GCHECK(wire_ready(&g, 0));
@@ -758,6 +894,7 @@ int run_party(node *self, config *c, int precision, int precision_p2, struct tim
 error:
 	if(g.grp) p1_group_sync(g.grp);
 	if(data) p1_gdata_free(data);
+	if(vals_host) p1_host_free(g.ctx, vals_host);
 	free(acc_host);
 	free(cols);
 	free(slots);

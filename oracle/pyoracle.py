@@ -134,6 +134,12 @@ class Oracle:
         col = np.ascontiguousarray(col)
         return int(self.lib.p1o_diag(_ptr(col), 1, col.size, precision, float(normalizer2), bits))
 
+    def downconvert(self, share, precision, precision_p2):
+        """64 -> 32 hand-off of a share word (src/phase1.c:609-620,629-635)"""
+        self.lib.p1o_downconvert.argtypes = [c_u64, c_i, c_i]
+        self.lib.p1o_downconvert.restype = c_u64
+        return int(self.lib.p1o_downconvert(int(share) & (2 ** 64 - 1), precision, precision_p2))
+
     def prg(self, key, byte_offset, nbytes):
         out = np.empty(nbytes, dtype=np.uint8)
         self.lib.p1o_prg(key, byte_offset, _ptr(out), nbytes)

@@ -150,3 +150,64 @@ def test_run_party_accepts_tokens_the_gpu_parser_defers(p1lib, tmp_path):
     open(path, "w").write("\n".join(text))
     (rs, _, _), (gs, _, _) = both(path, d, len(cs), 64, 64, 56, 0, False)
     assert np.array_equal(gs, rs)
+
+
+def _seeded_party_key(ti_key, node):
+    """K_p of host/phase1_gpu.c (seeded masks): SHA-256(label || K || LE32(node index))[0..16)"""
+    import hashlib
+    return hashlib.sha256(b"linreg-mpc p1gpu seeded mask key" + bytes(ti_key) + int(node).to_bytes(4, "little")).digest()[:16]
+
+
+@pytest.mark.parametrize("ndev", [1, 2])
+@pytest.mark.parametrize("b1,b2,prec,prec2", CASES)
+def test_run_party_seeded_masks(p1lib, oracle, tmp_path, monkeypatch, ndev, b1, b2, prec, prec2):
+    """P1GPU_SEEDED_MASKS=1 (host half): the TI ships one 16-byte key per provider and then only the
+    value of every pair; the providers expand their own mask on the GPU.  Checked word for word against the
+    oracle's restatement of the seeded definition (x under the key of b, y under the key of a, r under the TI's
+    key, same stream positions; share algebra of src/phase1.c:186-196,201-222), every other word against the
+    reference's phase1.c; the TI's sockets carry O(1) bytes per pair."""
+    if not (po.RefLib.available(b1, b2) and po.RefLib.available(b1, b2, gpuhost=True)):
+        pytest.skip("oracle/_ref was not prebuilt (needs the reference sources: build container only)")
+    monkeypatch.setenv("P1GPU_BATCH", "3")
+    if ndev > 1:
+        monkeypatch.setenv("P1GPU_DEVICES", _devices(ndev))
+    n, d, cs = 1500, 12, [0, 4, 8]
+    X, y, _ = po.generate_lin_regression(n, d, seed=29)
+    path = str(tmp_path / "inst.in")
+    po.write_instance(path, X, y, cs)
+    ref = po.RefLib(b1, b2)
+    rs, _, rsent = ref.run(path, d, len(cs), prec, prec2, use_ot=False)
+    monkeypatch.setenv("P1GPU_SEEDED_MASKS", "1")
+    gs, _, gsent = po.RefLib(b1, b2, gpuhost=True).run(path, d, len(cs), prec, prec2, use_ot=False)
+    Xw, yw, _ = ref.read_inputs(path, n, d, prec)
+    dt = po.word_dtype(b1)
+    Xw, yw = Xw.astype(dt), yw.astype(dt)
+    col = lambda c: yw if c == d else np.ascontiguousarray(Xw[:, c])
+    sch = oracle.schedule(d, cs)
+    nA = d * (d + 1) // 2
+    mask = (1 << b1) - 1
+    fin = (lambda v: oracle.downconvert(v, prec, prec2)) if b1 != b2 else (lambda v: v & mask)
+    want = rs.copy()
+    cross = 0
+    with np.errstate(over="ignore"):
+        for i, j, oi, oj, kind, q in zip(sch["i"], sch["j"], sch["owner_i"], sch["owner_j"], sch["kind"], sch["q"]):
+            if kind != 2:
+                continue
+            cross += 1
+            a, b = col(int(i)), col(int(j))
+            xo = oracle.ti_pair(_seeded_party_key(po.TI_KEY, oj + 2), int(q), n, b1)[0]
+            yo = oracle.ti_pair(_seeded_party_key(po.TI_KEY, oi + 2), int(q), n, b1)[1]
+            r = oracle.ti_pair(po.TI_KEY, int(q), n, b1)[3]
+            slot = int(i) * (int(i) + 1) // 2 + int(j) if i < d else nA + int(j)
+            sa = (oracle.dot(b + xo, yo, b1) - (oracle.dot(xo, yo, b1) - r)) & mask
+            sb = (oracle.dot(a - yo, b, b1) - r) & mask
+            want[oi, slot] = fin(sa)
+            want[oj, slot] = fin(sb)
+    assert cross > 0
+    assert np.array_equal(gs, want)
+    if b1 == b2:   # the sum over the parties does not depend on the masks: the reference's, word for word
+        assert np.array_equal(gs.sum(axis=0) & np.uint64(mask), rs.sum(axis=0) & np.uint64(mask))
+    # the TI's sockets: a key per provider and <= 8 + 11 bytes per message, against ~9.5 n per message
+    ti_bytes = int(gsent[0].sum())
+    assert ti_bytes <= len(cs) * (8 + 16) + 2 * cross * (8 + 11)
+    assert ti_bytes * 100 < int(rsent[0].sum())

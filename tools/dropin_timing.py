@@ -20,7 +20,7 @@ sys.path.insert(0, ROOT)
 from oracle import pyoracle as po  # noqa: E402
 
 
-def measure(n, d, providers, use_ot=False, bits=64, devices=None):
+def measure(n, d, providers, use_ot=False, bits=64, devices=None, seeded=False):
     """one instance file through the drop-in host file (cold, then warm) and through the reference's phase1.c"""
     prec = 56 if bits == 64 else 24
     X, y, _ = po.generate_lin_regression(n, d, seed=31)
@@ -29,18 +29,29 @@ def measure(n, d, providers, use_ot=False, bits=64, devices=None):
     po.Oracle().write_instance(path, X, y, cs)
     if devices:
         os.environ["P1GPU_DEVICES"] = devices
+    if seeded:
+        os.environ["P1GPU_SEEDED_MASKS"] = "1"      # read by the drop-in host file only (the reference has no such mode)
     out = {"n": n, "d": d, "providers": providers, "use_ot": use_ot, "bits": bits,
            "devices": os.environ.get("P1GPU_DEVICES", os.environ.get("P1GPU_DEVICE", "0")),
            "text_bytes": os.path.getsize(path)}
-    res = {}
+    res, sent_by = {}, {}
     for name, gpuhost in (("gpu_host", True), ("gpu_host_warm", True), ("reference_phase1_c", False)):
         lib = po.RefLib(bits, bits, gpuhost=gpuhost)
         t0 = time.perf_counter()
         shares, stats, sent = lib.run(path, d, providers, prec, 0, use_ot=use_ot)
         res[name] = shares
+        sent_by[name] = sent
         out[name + "_s"] = time.perf_counter() - t0
         out[name + "_bytes_on_sockets"] = int(sent.sum())
     os.remove(path)
+    out["seeded_masks"] = bool(seeded)
+    if seeded:
+        # other masks than the reference's single stream: the shares differ word by word, their sum over the parties
+        # (what phase 2 consumes) does not; tests/test_gpu_dropin.py::test_run_party_seeded_masks checks every word
+        m = np.uint64((1 << bits) - 1)
+        out["share_sums_identical"] = bool(np.array_equal(res["gpu_host_warm"].sum(axis=0) & m, res["reference_phase1_c"].sum(axis=0) & m))
+        out["ti_bytes_on_sockets"] = int(sent_by["gpu_host_warm"][0].sum())
+        out["reference_ti_bytes_on_sockets"] = int(sent_by["reference_phase1_c"][0].sum())
     out["shares_identical"] = bool(np.array_equal(res["gpu_host_warm"], res["reference_phase1_c"]) and
                                    np.array_equal(res["gpu_host"], res["reference_phase1_c"]))
     out["speedup_warm"] = out["reference_phase1_c_s"] / out["gpu_host_warm_s"]
@@ -61,8 +72,9 @@ def main():
     ap.add_argument("--use-ot", action="store_true")
     ap.add_argument("--bits", type=int, default=64)
     ap.add_argument("--devices", default=None, help="P1GPU_DEVICES for the drop-in's parties, e.g. 0,1")
+    ap.add_argument("--seeded", action="store_true", help="P1GPU_SEEDED_MASKS=1: the TI sends keys and values, the providers expand their masks")
     args = ap.parse_args()
-    print(json.dumps(measure(args.n, args.d, args.providers, args.use_ot, args.bits, args.devices)))
+    print(json.dumps(measure(args.n, args.d, args.providers, args.use_ot, args.bits, args.devices, args.seeded)))
 
 
 if __name__ == "__main__":
