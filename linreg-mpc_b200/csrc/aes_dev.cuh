@@ -193,21 +193,27 @@ __device__ __forceinline__ void aes_ctr_group(const AesCtrKey &K, uint32_t lb, u
 	G.id = lo >> 8;
 }
 
+// keystream block of the group G caches (block >> 32 == K.hi and (uint32_t) block >> 8 == G.id): 1 + 4 lookups for
+// rounds 1-2, then rounds 3-10
+__device__ __forceinline__ void aes_ctr_block_in_group(const AesCtrKey &K, uint32_t lb, uint32_t lo, const AesCtrGroup &G, uint32_t s[4]) {
+	const AesConstKey rk(K.k);
+	const uint32_t s3 = __byte_perm(lo, 0, 0x0123) ^ K.k.rk[3];
+	const uint32_t t0 = K.c1[0] ^ aes_lk<3, 3>(s3, lb);
+	const uint32_t u0 = G.g[0] ^ aes_lk<0, 0>(t0, lb);
+	const uint32_t u1 = G.g[1] ^ aes_lk<3, 3>(t0, lb);
+	const uint32_t u2 = G.g[2] ^ aes_lk<2, 2>(t0, lb);
+	const uint32_t u3 = G.g[3] ^ aes_lk<1, 1>(t0, lb);
+	aes_rounds_to_10<3>(rk, lb, u0, u1, u2, u3, s);
+}
+
 // keystream block through the group cache G (one cache per stream a lane walks)
 __device__ __forceinline__ void aes_ctr_block_g(const AesCtrKey &K, uint32_t lb, uint64_t block, AesCtrGroup &G, uint32_t s[4]) {
-	const AesConstKey rk(K.k);
 	const uint32_t lo = (uint32_t) block;
 	if((uint32_t) (block >> 32) == K.hi) {
 		if((lo >> 8) != G.id) aes_ctr_group(K, lb, lo, G);
-		const uint32_t s3 = __byte_perm(lo, 0, 0x0123) ^ K.k.rk[3];
-		const uint32_t t0 = K.c1[0] ^ aes_lk<3, 3>(s3, lb);
-		const uint32_t u0 = G.g[0] ^ aes_lk<0, 0>(t0, lb);
-		const uint32_t u1 = G.g[1] ^ aes_lk<3, 3>(t0, lb);
-		const uint32_t u2 = G.g[2] ^ aes_lk<2, 2>(t0, lb);
-		const uint32_t u3 = G.g[3] ^ aes_lk<1, 1>(t0, lb);
-		aes_rounds_to_10<3>(rk, lb, u0, u1, u2, u3, s);
+		aes_ctr_block_in_group(K, lb, lo, G, s);
 	} else {
-		aes_ctr_block_k(rk, lb, block, s);
+		aes_ctr_block_k(AesConstKey(K.k), lb, block, s);
 	}
 }
 

@@ -34,6 +34,7 @@ struct FusedParams {
 	void *x, *y;           // optional: the masks themselves
 	uint64_t *xy, *r, *acc;
 	uint32_t units_per_pair;
+	uint32_t opt_fast;     // 0: every unit through the general loop (ctx option "fused_fast", for comparisons)
 	const uint32_t *T0;
 };
 
@@ -161,6 +162,61 @@ __device__ __forceinline__ void fu_full(FuPair<W> &S, int64_t o, const uint32_t 
 	}
 }
 
+// The common case as a loop of its own: 64-bit ring, x and y streams 16 bytes apart modulo 16 (n_total even), a
+// work unit (one 256-block group of the x stream) that lies wholly inside the shard's mask and inside one 2^32-block
+// span of the counter for both streams, masks not materialised.  No bounds tests, no cross-lane traffic: for odd
+// pairs (HW = 2: a block starts 8 bytes into a 16-byte line of the row arrays) a lane reads and writes its two rows
+// as two 8-byte accesses instead of joining half lines with its neighbour.  The provider columns of iteration i+1
+// are on their way while the two AES blocks of iteration i are computed.
+template <int HW>
+__device__ __forceinline__ void fu_fast_unit(const FusedParams &P, uint32_t lb, FuPair<uint64_t> &S, uint64_t k,
+	uint32_t lox, uint32_t loy, AesCtrGroup &gx, AesCtrGroup &gy) {
+	const uint64_t *pa = S.a + k, *pb = S.b + k;
+	uint64_t *pmb = S.mb + k, *pma = S.ma + k;
+	uint64_t an[2], bn[2];
+	if(HW == 0) {
+		FuLine<uint64_t>::load(pa, an);
+		FuLine<uint64_t>::load(pb, bn);
+	} else {
+		an[0] = __ldg(pa); an[1] = __ldg(pa + 1);
+		bn[0] = __ldg(pb); bn[1] = __ldg(pb + 1);
+	}
+	aes_ctr_group(P.key, lb, lox, gx);          // the unit is one group of the x stream
+#pragma unroll 1
+	for(int i = 0; i < FU_U; i++) {
+		const uint64_t a0 = an[0], a1 = an[1], b0 = bn[0], b1 = bn[1];
+		if(i + 1 < FU_U) {
+			pa += 64; pb += 64;                  // 32 blocks = 512 bytes on
+			if(HW == 0) {
+				FuLine<uint64_t>::load(pa, an);
+				FuLine<uint64_t>::load(pb, bn);
+			} else {
+				an[0] = __ldg(pa); an[1] = __ldg(pa + 1);
+				bn[0] = __ldg(pb); bn[1] = __ldg(pb + 1);
+			}
+		}
+		uint32_t xs[4], ys[4];
+		aes_ctr_block_in_group(P.key, lb, lox, gx, xs);
+		if((loy >> 8) != gy.id) aes_ctr_group(P.key, lb, loy, gy);
+		aes_ctr_block_in_group(P.key, lb, loy, gy, ys);
+		lox += 32; loy += 32;
+		const uint64_t x0 = ((uint64_t) xs[1] << 32) | xs[0], x1 = ((uint64_t) xs[3] << 32) | xs[2];
+		const uint64_t y0 = ((uint64_t) ys[1] << 32) | ys[0], y1 = ((uint64_t) ys[3] << 32) | ys[2];
+		const uint64_t mb0 = b0 + x0, mb1 = b1 + x1, ma0 = a0 - y0, ma1 = a1 - y1;
+		S.dxy += x0 * y0 + x1 * y1;
+		S.da += mb0 * y0 + mb1 * y1;
+		S.db += ma0 * b0 + ma1 * b1;
+		if(HW == 0) {
+			__stcs(reinterpret_cast<ulonglong2 *>(pmb), make_ulonglong2(mb0, mb1));
+			__stcs(reinterpret_cast<ulonglong2 *>(pma), make_ulonglong2(ma0, ma1));
+		} else {
+			__stcs(pmb, mb0); __stcs(pmb + 1, mb1);
+			__stcs(pma, ma0); __stcs(pma + 1, ma1);
+		}
+		pmb += 64; pma += 64;
+	}
+}
+
 template <typename W, bool ALIGNED, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams P) {
 	extern __shared__ __align__(256) uint8_t smem[];
@@ -196,6 +252,19 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 		const uint64_t B0 = (b_first & ~(uint64_t) 255) + (uint64_t) uu * (32 * FU_U);
 		// offset of the block group in the shard's mask; the phase (o & 15) is the same for every block of the pair
 		const uint32_t hw = ((uint32_t) X0 & 15u) >> 2;   // words of a block that complete the line begun by the block before
+		if constexpr(w == 8 && ALIGNED) {
+			// warp-uniform: the whole unit inside the mask, one high counter word for both streams, masks not kept
+			const int64_t o0 = (int64_t) (B0 << 4) - (int64_t) X0;
+			const uint64_t By0 = B0 + (ydelta >> 4);
+			if(!P.x && !P.y && P.opt_fast && o0 >= 0 && o0 + 16 * 32 * FU_U <= (int64_t) nbytes
+				&& (uint32_t) (B0 >> 32) == P.key.hi && (uint32_t) ((B0 + 32 * FU_U - 1) >> 32) == P.key.hi
+				&& (uint32_t) (By0 >> 32) == P.key.hi && (uint32_t) ((By0 + 32 * FU_U - 1) >> 32) == P.key.hi) {
+				const uint64_t k = ((uint64_t) o0 >> 3) + 2 * lane;
+				if(hw == 0) fu_fast_unit<0>(P, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+				else fu_fast_unit<2>(P, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+				goto unit_done;
+			}
+		}
 #pragma unroll 1
 		for(int i = 0; i < FU_U; i++) {
 			const uint64_t B = B0 + i * 32 + lane;
@@ -248,6 +317,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 				fu_elem<W>(S, (uint64_t) ob / w, xv, yv);
 			}
 		}
+	unit_done:
 		S.dxy = p1_warp_sum(S.dxy);
 		S.da = p1_warp_sum(S.da);
 		S.db = p1_warp_sum(S.db);
@@ -340,6 +410,7 @@ extern "C" int p1_masking_fused(p1_ctx *ctx, const uint8_t key[16], uint64_t q0,
 	P.xy = xy_dev;
 	P.r = r_dev;
 	P.acc = acc_dev;
+	P.opt_fast = ctx->opt_fused_fast ? 1u : 0u;
 	const uint64_t nblk = ((uint64_t) n_rows * w + 15 + 15) / 16;
 	P.units_per_pair = (uint32_t) ((nblk + 255 + 32 * FU_U - 1) / (32 * FU_U));
 	P1_CUDA(cudaMemsetAsync(xy_dev, 0, count * sizeof(uint64_t), ctx->stream));
