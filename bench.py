@@ -333,8 +333,11 @@ def main():
     torch.cuda.synchronize()
 
     gram = {"auto": pkg.ffi.P1_GRAM_AUTO, "imad": pkg.ffi.P1_GRAM_IMAD, "tcgen05": pkg.ffi.P1_GRAM_TCGEN05}[args.gram]
-    # pairs per launch: the fused loop keeps two message buffers per pipe (<= 1 GB each), the split kernels four (<= 256 MB each)
-    batch = args.batch_pairs or max(1, min(256, ((1 << 30) if args.aggregation == "masking" else (256 << 20)) // max(1, n_rows * w)))
+    # pairs per launch: the fused loop keeps two message buffers per pipe (<= 1 GB each), the split kernels four (<= 256 MB each).
+    # Row shards get proportionally more pairs per launch (up to 2048): a launch of the persistent grid should hold
+    # many work units per warp, or its last round of units leaves SMs idle (245 units per pair at 125k rows)
+    fused_step = args.aggregation == "masking"
+    batch = args.batch_pairs or max(1, min(2048 if fused_step else 256, ((1 << 30) if fused_step else (256 << 20)) // max(1, n_rows * w)))
     box = Phase1Box(lib, n, d, cs, wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
                     row0=row0, n_rows=n_rows, batch_pairs=batch, pipes=args.pipes, gram_algo=gram, group=group)
     for o in args.opt:
