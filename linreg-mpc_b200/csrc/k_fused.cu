@@ -21,7 +21,7 @@
 #define FU_THREADS 512
 
 struct FusedParams {
-	AesCtrKey key;
+	AesCtrKey key, keyb;   // keyb: the same key with round 1 folded for the NEXT 2^32-block span of the counter (hi + 1)
 	uint64_t q0;
 	uint32_t count;
 	uint64_t n_total, row0, n_rows;
@@ -169,7 +169,7 @@ __device__ __forceinline__ void fu_full(FuPair<W> &S, int64_t o, const uint32_t 
 // as two 8-byte accesses instead of joining half lines with its neighbour.  The provider columns of iteration i+1
 // are on their way while the two AES blocks of iteration i are computed.
 template <int HW>
-__device__ __forceinline__ void fu_fast_unit(const FusedParams &P, uint32_t lb, FuPair<uint64_t> &S, uint64_t k,
+__device__ __forceinline__ void fu_fast_unit(const FusedParams &P, const AesCtrKey &K, uint32_t lb, FuPair<uint64_t> &S, uint64_t k,
 	uint32_t lox, uint32_t loy, AesCtrGroup &gx, AesCtrGroup &gy) {
 	const uint64_t *pa = S.a + k, *pb = S.b + k;
 	uint64_t *pmb = S.mb + k, *pma = S.ma + k;
@@ -181,7 +181,7 @@ __device__ __forceinline__ void fu_fast_unit(const FusedParams &P, uint32_t lb, 
 		an[0] = __ldg(pa); an[1] = __ldg(pa + 1);
 		bn[0] = __ldg(pb); bn[1] = __ldg(pb + 1);
 	}
-	aes_ctr_group(P.key, lb, lox, gx);          // the unit is one group of the x stream
+	aes_ctr_group(K, lb, lox, gx);          // the unit is one group of the x stream
 #pragma unroll 1
 	for(int i = 0; i < FU_U; i++) {
 		const uint64_t a0 = an[0], a1 = an[1], b0 = bn[0], b1 = bn[1];
@@ -196,9 +196,9 @@ __device__ __forceinline__ void fu_fast_unit(const FusedParams &P, uint32_t lb, 
 			}
 		}
 		uint32_t xs[4], ys[4];
-		aes_ctr_block_in_group(P.key, lb, lox, gx, xs);
-		if((loy >> 8) != gy.id) aes_ctr_group(P.key, lb, loy, gy);
-		aes_ctr_block_in_group(P.key, lb, loy, gy, ys);
+		aes_ctr_block_in_group(K, lb, lox, gx, xs);
+		if((loy >> 8) != gy.id) aes_ctr_group(K, lb, loy, gy);
+		aes_ctr_block_in_group(K, lb, loy, gy, ys);
 		lox += 32; loy += 32;
 		const uint64_t x0 = ((uint64_t) xs[1] << 32) | xs[0], x1 = ((uint64_t) xs[3] << 32) | xs[2];
 		const uint64_t y0 = ((uint64_t) ys[1] << 32) | ys[0], y1 = ((uint64_t) ys[3] << 32) | ys[2];
@@ -233,6 +233,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 	const uint32_t ysh = (uint32_t) (ydelta & 15);
 	AesCtrGroup gx, gy, gy1;
 	gx.id = gy.id = gy1.id = 0xffffffffu;
+	uint32_t last_hi = P.key.hi;      // high counter word the group caches were computed for
 
 	for(uint32_t u = gw; u < units; u += warps_total) {
 		const uint32_t p = u / P.units_per_pair, uu = u - p * P.units_per_pair;
@@ -253,17 +254,28 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 		// offset of the block group in the shard's mask; the phase (o & 15) is the same for every block of the pair
 		const uint32_t hw = ((uint32_t) X0 & 15u) >> 2;   // words of a block that complete the line begun by the block before
 		if constexpr(w == 8 && ALIGNED) {
-			// warp-uniform: the whole unit inside the mask, one high counter word for both streams, masks not kept
+			// warp-uniform: the whole unit inside the mask, one high counter word for both streams - the one the launch
+			// started in (key) or the next (keyb: a launch of many pairs may cross a multiple of 2^32 blocks) -, masks not kept
 			const int64_t o0 = (int64_t) (B0 << 4) - (int64_t) X0;
 			const uint64_t By0 = B0 + (ydelta >> 4);
+			const uint32_t hiw = (uint32_t) (B0 >> 32);
 			if(!P.x && !P.y && P.opt_fast && o0 >= 0 && o0 + 16 * 32 * FU_U <= (int64_t) nbytes
-				&& (uint32_t) (B0 >> 32) == P.key.hi && (uint32_t) ((B0 + 32 * FU_U - 1) >> 32) == P.key.hi
-				&& (uint32_t) (By0 >> 32) == P.key.hi && (uint32_t) ((By0 + 32 * FU_U - 1) >> 32) == P.key.hi) {
+				&& (hiw == P.key.hi || hiw == P.keyb.hi) && (uint32_t) ((B0 + 32 * FU_U - 1) >> 32) == hiw
+				&& (uint32_t) (By0 >> 32) == hiw && (uint32_t) ((By0 + 32 * FU_U - 1) >> 32) == hiw) {
 				const uint64_t k = ((uint64_t) o0 >> 3) + 2 * lane;
-				if(hw == 0) fu_fast_unit<0>(P, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
-				else fu_fast_unit<2>(P, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+				// the group caches belong to one (key, hi): drop them when the unit uses the other
+				if(hiw != last_hi) { gx.id = gy.id = gy1.id = 0xffffffffu; last_hi = hiw; }
+				if(hiw == P.key.hi) {
+					if(hw == 0) fu_fast_unit<0>(P, P.key, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+					else fu_fast_unit<2>(P, P.key, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+				} else {
+					if(hw == 0) fu_fast_unit<0>(P, P.keyb, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+					else fu_fast_unit<2>(P, P.keyb, lb, S, k, (uint32_t) B0 + lane, (uint32_t) By0 + lane, gx, gy);
+				}
 				goto unit_done;
 			}
+			// the general loop caches groups of key.hi only
+			if(last_hi != P.key.hi) { gx.id = gy.id = gy1.id = 0xffffffffu; last_hi = P.key.hi; }
 		}
 #pragma unroll 1
 		for(int i = 0; i < FU_U; i++) {
@@ -385,7 +397,9 @@ extern "C" int p1_masking_fused(p1_ctx *ctx, const uint8_t key[16], uint64_t q0,
 	P1_CHECK(count <= 0xffffffffu, "p1_masking_fused: batch too large");
 	FusedParams P;
 	if(aes_device_T0(ctx, &P.T0)) return 1;
-	aes_host_ctr_key(key, (uint32_t) ((((uint64_t) q0 * (2 * (uint64_t) n_total + 1) + row0) * w) >> 36), &P.key);
+	const uint32_t hi0 = (uint32_t) ((((uint64_t) q0 * (2 * (uint64_t) n_total + 1) + row0) * w) >> 36);
+	aes_host_ctr_key(key, hi0, &P.key);
+	aes_host_ctr_key(key, hi0 + 1, &P.keyb);
 	const void *ca = NULL, *cb = NULL, *sa = NULL, *sb = NULL;
 	if(p1_small_to_dev(ctx, cols_a, count * sizeof(int32_t), 0, &ca)) return 1;
 	if(p1_small_to_dev(ctx, cols_b, count * sizeof(int32_t), 1, &cb)) return 1;

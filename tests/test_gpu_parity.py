@@ -535,10 +535,25 @@ def test_masking_fused_parity(p1lib, oracle, bits, n_total, row0, n_rows):
     """the one-kernel masking loop (p1_masking_fused): both party messages, the masks when kept, <x,y>, r
     and both share sums equal the oracle's TI stream + party algebra (src/phase1.c:173-224,270-278), for
     every phase of a pair's mask inside the 16-byte AES blocks (odd pairs, odd n, row shards)"""
+    _masking_fused_case(p1lib, oracle, bits, n_total, row0, n_rows, 7)
+
+
+@pytest.mark.parametrize("bits", [64, 32])
+def test_masking_fused_counter_crosses_2_32_blocks(p1lib, oracle, bits):
+    """a launch whose pairs straddle a multiple of 2^32 keystream blocks: pairs before it run under the key folded
+    for the launch's first high counter word, the pair that contains it through the general loop, pairs after it
+    under the key folded for the next one (k_fused.cu: key / keyb)"""
+    n_total = 70000
+    per_pair = (2 * n_total + 1) * (bits // 8)               # keystream bytes per pair
+    q_cross = (16 << 32) // per_pair                         # the pair that contains block 2^32
+    _masking_fused_case(p1lib, oracle, bits, n_total, 512, 66000, q_cross - 2)
+
+
+def _masking_fused_case(p1lib, oracle, bits, n_total, row0, n_rows, q0):
     ctx = mkctx(p1lib, bits, bits)
     rng = np.random.default_rng(80 + n_total)
     dt = po.word_dtype(bits)
-    d, q0, count = 5, 7, 6
+    d, count = 5, 6
     Xw = rng.integers(0, 2 ** 63, (n_rows, d), dtype=np.uint64).astype(dt)
     yw = rng.integers(0, 2 ** 63, n_rows, dtype=np.uint64).astype(dt)
     data = from_words(p1lib, ctx, Xw, yw)
