@@ -533,6 +533,8 @@ def main():
         try:   # DRAM bytes per launch of this kernel from the committed ncu --set full capture, if the shape matches
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 tr = json.load(f).get(dominant)
+            if tr and "lsu_bound" in roofline and tr.get("l1tex_data_stage"):
+                roofline["lsu_bound"] = dict(roofline["lsu_bound"], ncu_l1tex_data_stage=tr["l1tex_data_stage"])
             if tr and tr.get("pairs") is None:
                 roofline["traffic"] = tr["bytes_per_launch"]
                 roofline["traffic_source"] = tr["source"]

@@ -522,9 +522,9 @@ int run_trusted_initializer(node *self, config *c, int precision, bool use_ot) {
 			const uint64_t *va = vals_host + (size_t) set * 2 * g.batch, *vb = va + g.batch;
 			for(size_t p = 0; p < cur.count; p++) {
 				uint8_t m[16];
-				size_t len = value_msg_encode(va[p], m);
+				size_t len = value_msg_encode((ufixed_p1_t) va[p], m);        /* the field has the ring's width */
 				check(!send_wire(self->peer[cur.owner_i], m, len), "Could not send message to party A (%d)", cur.owner_i);
-				len = value_msg_encode(vb[p], m);
+				len = value_msg_encode((ufixed_p1_t) vb[p], m);
 				check(!send_wire(self->peer[cur.owner_j], m, len), "Could not send message to party B (%d)", cur.owner_j);
 			}
 			t_send += now_s() - t0;
