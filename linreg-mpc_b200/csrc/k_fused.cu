@@ -34,6 +34,7 @@ struct FusedParams {
 	void *x, *y;           // optional: the masks themselves
 	uint64_t *xy, *r, *acc;
 	uint32_t units_per_pair;
+	uint32_t chunk;        // consecutive work units a warp takes at a time (ctx option "fused_chunk")
 	uint32_t opt_fast;     // 0: every unit through the general loop (ctx option "fused_fast", for comparisons)
 	const uint32_t *T0;
 };
@@ -235,8 +236,35 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 	gx.id = gy.id = gy1.id = 0xffffffffu;
 	uint32_t last_hi = P.key.hi;      // high counter word the group caches were computed for
 
-	for(uint32_t u = gw; u < units; u += warps_total) {
+	// A warp takes `chunk` consecutive units at a time: they mostly belong to one pair, so the three running sums are
+	// reduced over the warp and added to memory once per chunk instead of once per unit, and the y-stream group of a
+	// unit's last blocks is still cached when the next unit starts.
+	// Whole rounds of chunks (every warp gets the same number) first, the remaining units one at a time, so that the
+	// last round of a launch is no longer than one unit.
+	const uint32_t chunk = P.chunk;
+	const uint32_t full_chunks = units / (chunk * warps_total) * warps_total;     // chunks in whole rounds
+	const uint32_t U1 = full_chunks * chunk, items = full_chunks + (units - U1);
+	uint32_t cur_p = 0xffffffffu;
+	uint64_t sxy = 0, sa = 0, sb = 0;
+	auto flush = [&]() {
+		if(cur_p == 0xffffffffu) return;
+		sxy = p1_warp_sum(sxy);
+		sa = p1_warp_sum(sa);
+		sb = p1_warp_sum(sb);
+		if(lane == 0) {
+			if(sxy) p1_red_add(P.xy + cur_p, sxy);
+			if(sa) p1_red_add(P.acc + P.slots_a[cur_p], sa);
+			if(sb) p1_red_add(P.acc + P.slots_b[cur_p], sb);
+		}
+		sxy = sa = sb = 0;
+	};
+	for(uint32_t it = gw; it < items; it += warps_total)
+	for(uint32_t u = it < full_chunks ? it * chunk : U1 + (it - full_chunks), u_end = it < full_chunks ? u + chunk : u + 1; u < u_end; u++) {
 		const uint32_t p = u / P.units_per_pair, uu = u - p * P.units_per_pair;
+		if(p != cur_p) {
+			flush();
+			cur_p = p;
+		}
 		const uint64_t W0 = (P.q0 + p) * (2 * P.n_total + 1);
 		const uint64_t X0 = (W0 + P.row0) * w;
 		const uint64_t b_first = X0 >> 4;
@@ -247,7 +275,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 		S.ma = (W *) P.msg_a + (uint64_t) p * P.ld;
 		S.xo = P.x ? (W *) P.x + (uint64_t) p * P.ld : nullptr;
 		S.yo = P.y ? (W *) P.y + (uint64_t) p * P.ld : nullptr;
-		S.dxy = S.da = S.db = 0;
+		S.dxy = sxy; S.da = sa; S.db = sb;
 		uint32_t cx[4] = {0, 0, 0, 0}, cy[4] = {0, 0, 0, 0};
 		bool carry = false;
 		const uint64_t B0 = (b_first & ~(uint64_t) 255) + (uint64_t) uu * (32 * FU_U);
@@ -330,14 +358,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 			}
 		}
 	unit_done:
-		S.dxy = p1_warp_sum(S.dxy);
-		S.da = p1_warp_sum(S.da);
-		S.db = p1_warp_sum(S.db);
-		if(lane == 0) {
-			if(S.dxy) p1_red_add(P.xy + p, S.dxy);
-			if(S.da) p1_red_add(P.acc + P.slots_a[p], S.da);
-			if(S.db) p1_red_add(P.acc + P.slots_b[p], S.db);
-		}
+		sxy = S.dxy; sa = S.da; sb = S.db;
 		if(P.r && uu == 0) {
 			// r = S[W0 + 2 n_total] (src/phase1.c:273)
 			const uint64_t Rb = (W0 + 2 * P.n_total) * w;
@@ -353,6 +374,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_masking_fused(const FusedParams 
 			if(lane == 0) P.r[p] = ((uint64_t) hi << 32) | lo;
 		}
 	}
+	flush();
 }
 
 template <typename W, bool ALIGNED, int THREADS>
@@ -362,7 +384,7 @@ static int launch_fused_t(p1_ctx *ctx, const FusedParams &P) {
 	const uint64_t units = (uint64_t) P.count * P.units_per_pair;
 	P1_CHECK(units < 0xffffffffull, "p1_masking_fused: batch too large (%llu work units)", (unsigned long long) units);
 	uint64_t grid = (uint64_t) ctx->sm_count;
-	const uint64_t need = (units + THREADS / 32 - 1) / (THREADS / 32);
+	const uint64_t need = (units + THREADS / 32 - 1) / (THREADS / 32);   // small launches: one unit per warp
 	if(grid > need) grid = need;
 	p1_prof_begin(ctx, P1_K_MASKING_FUSED);
 	k_masking_fused<W, ALIGNED, THREADS><<<(unsigned) grid, THREADS, smem, ctx->stream>>>(P);
@@ -425,6 +447,7 @@ extern "C" int p1_masking_fused(p1_ctx *ctx, const uint8_t key[16], uint64_t q0,
 	P.r = r_dev;
 	P.acc = acc_dev;
 	P.opt_fast = ctx->opt_fused_fast ? 1u : 0u;
+	P.chunk = ctx->opt_fused_chunk > 0 ? (uint32_t) ctx->opt_fused_chunk : 8u;
 	const uint64_t nblk = ((uint64_t) n_rows * w + 15 + 15) / 16;
 	P.units_per_pair = (uint32_t) ((nblk + 255 + 32 * FU_U - 1) / (32 * FU_U));
 	P1_CUDA(cudaMemsetAsync(xy_dev, 0, count * sizeof(uint64_t), ctx->stream));

@@ -182,6 +182,7 @@ extern "C" int p1_ctx_create(int device, int ring_bits_p1, int ring_bits_p2, p1_
 	ctx->opt_ti_threads = 0;
 	ctx->opt_fused_threads = 0;
 	ctx->opt_fused_fast = 1;
+	ctx->opt_fused_chunk = 0;
 	ctx->opt_encode_planes = 0;
 	ctx->opt_encode_async = 1;
 	ctx->prof = false;
@@ -264,6 +265,10 @@ extern "C" int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value) {
 	else if(!strcmp(name, "gram_tc_min_cols")) ctx->opt_tc_min_cols = value;
 	else if(!strcmp(name, "gram_tc_whole")) ctx->opt_tc_whole = value;
 	else if(!strcmp(name, "fused_fast")) ctx->opt_fused_fast = value;
+	else if(!strcmp(name, "fused_chunk")) {
+		P1_CHECK(value >= 0 && value <= 4096, "fused_chunk must be in [0, 4096] (0 = default)");
+		ctx->opt_fused_chunk = value;
+	}
 	else if(!strcmp(name, "ti_threads")) {
 		P1_CHECK(value == 0 || (value % 32 == 0 && value >= 32 && value <= 512), "ti_threads must be a multiple of 32 in [32,512]");
 		ctx->opt_ti_threads = value;

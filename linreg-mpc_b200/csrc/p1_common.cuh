@@ -29,7 +29,7 @@ struct p1_ctx {
 	void *limb_ws;  size_t limb_ws_bytes;
 	// tile sums / offsets of the wire-format kernels (k_wire.cu), grown on demand
 	void *wire_ws;  size_t wire_ws_bytes;
-	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols, opt_tc_whole, opt_fused_fast;
+	long opt_tc_max_slices, opt_tc_chunk_blocks, opt_tc_min_cols, opt_tc_whole, opt_fused_fast, opt_fused_chunk;
 	long opt_ti_threads;              // threads per CTA of k_ti_generate (0 = default)
 	long opt_fused_threads;           // threads per CTA of k_masking_fused (0 = default)
 	long opt_encode_async;            // encode through the cp.async pipeline (k_encode_async) when the layout allows
