@@ -86,7 +86,13 @@ const char *p1_kernel_class_name(int kernel_class);
  *   "gram_tc_chunk_blocks" : 128-row blocks accumulated in s32 before a drain (only lowered)
  *   "gram_tc_min_cols"     : P1_GRAM_AUTO picks the tcgen05 kernel from this block width on
  *   "ti_threads"           : threads per CTA of the persistent mask-expansion kernel (one CTA per SM)
- *   "fused_threads"        : same for the fused masking-loop kernel (p1_masking_fused)
+ *   "fused_threads"        : CTA size of the fused masking-loop kernel (p1_masking_fused): 0 = default (512), or one
+ *                            of the compiled sizes 384, 512, 640, 768, 1024 (each with its own register budget)
+ *   "fused_fast"           : 0 = every work unit of p1_masking_fused through the general loop (default 1: interior
+ *                            units of a 64-bit ring with n_total even take the straight loop; identical results)
+ *   "fused_chunk"          : consecutive work units a warp of p1_masking_fused takes at a time (0 = default 8)
+ *   "gram_tc_whole"        : 0 = one-digit blocks of <= 256 columns also use the tiled tcgen05 kernel (default 1:
+ *                            k_gram_whole, every CTA multiplies the whole block over its rows; identical results)
  *   "encode_async"         : 0 = never use the cp.async pipeline kernel of p1_encode (default 1: used whenever d
  *                            is even and the source is 16-byte aligned; identical results)
  *   "encode_planes"        : 1 = p1_encode also writes, in the same pass, the base-256 digit planes of ALL
