@@ -160,6 +160,17 @@ static int value_msg_decode(const uint8_t *in, size_t size, uint64_t *value) {
 	return 1;
 }
 
+#ifdef P1_WITH_BASE_OT_SELFTEST
+/* test hooks (the loop-back build of oracle/Makefile only; tests/test_host.py) */
+size_t p1host_selftest_value_msg(uint64_t value, uint8_t out[16], uint64_t *back, int *decode_status) {
+	const size_t len = value_msg_encode(value, out);
+	*decode_status = value_msg_decode(out, len, back);
+	return len;
+}
+int p1host_selftest_value_msg_decode(const uint8_t *in, size_t size, uint64_t *value) { return value_msg_decode(in, size, value); }
+void p1host_selftest_party_key(const uint8_t ti_key[16], int party, uint8_t out[16]) { seeded_party_key(ti_key, party, out); }
+#endif
+
 static int owner_of(size_t row, const config *c) {
 	int party = 0;
 	for(; party + 1 < c->num_parties && c->index_owned[party + 1] <= (ssize_t) row; party++);

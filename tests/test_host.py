@@ -185,3 +185,40 @@ def test_default_base_ot_provider_of_the_dropin():
     assert np.array_equal(np.where(bits[:, None], s1, s0), ss)
     assert not np.any(np.all(np.where(bits[:, None], s0, s1) == ss, axis=1))
     assert len({bytes(r) for r in np.concatenate([s0, s1])}) == 256
+
+
+def test_seeded_mask_messages_of_the_dropin():
+    """host/phase1_gpu.c with P1GPU_SEEDED_MASKS=1: the TI's value-only message is SecureMultiplication.Msg with an
+    empty vector (field 2, varint) and round-trips for every width; malformed messages are refused; the per-provider
+    key is SHA-256(label || K || LE32(p))[0..16)"""
+    import ctypes
+    import hashlib
+    path = os.path.join(ROOT, "oracle", "_ref", "libp1gpuhost_64_64.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libp1gpuhost_* is built only where the reference sources are present")
+    L = ctypes.CDLL(path)
+    L.p1host_selftest_value_msg.restype = ctypes.c_size_t
+    L.p1host_selftest_value_msg.argtypes = [ctypes.c_uint64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_int)]
+    L.p1host_selftest_value_msg_decode.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint64)]
+
+    def varint(v):
+        out = bytearray()
+        while True:
+            b = v & 0x7f
+            v >>= 7
+            out.append(b | (0x80 if v else 0))
+            if not v:
+                return bytes(out)
+    for v in (0, 1, 127, 128, 300, 2 ** 32 - 1, 2 ** 32, 2 ** 56 - 1, 2 ** 63, 2 ** 64 - 1):
+        buf = (ctypes.c_uint8 * 16)()
+        back, st = ctypes.c_uint64(), ctypes.c_int(-1)
+        n = L.p1host_selftest_value_msg(v, buf, ctypes.byref(back), ctypes.byref(st))
+        assert bytes(buf[:n]) == b"\x10" + varint(v) and st.value == 0 and back.value == v
+    val = ctypes.c_uint64()
+    for bad in (b"", b"\x10", b"\x08\x01", b"\x10\x80", b"\x10\x01\x01", b"\x10" + b"\xff" * 10 + b"\x01"):
+        assert L.p1host_selftest_value_msg_decode(bad, len(bad), ctypes.byref(val)) != 0, bad
+    key = bytes(range(16))
+    for party in (2, 3, 21):
+        out = (ctypes.c_uint8 * 16)()
+        L.p1host_selftest_party_key(key, party, out)
+        assert bytes(out) == hashlib.sha256(b"linreg-mpc p1gpu seeded mask key" + key + party.to_bytes(4, "little")).digest()[:16]
