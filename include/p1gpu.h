@@ -364,6 +364,30 @@ int p1_finalize_async(p1_ctx *ctx, const uint64_t *acc_dev, size_t num, size_t d
 size_t p1_msg_max_bytes(const p1_ctx *ctx, size_t n_words);
 int p1_msg_pack(p1_ctx *ctx, const void *vec_dev, size_t ld_words, size_t n_words, size_t count,
                 const uint64_t *values, uint8_t *out_dev, size_t stride_bytes, uint64_t *sizes_dev);
+/* p1_msg_pack for callers that must not allocate.  (No counterpart in the reference: it is the same
+ * pack_to_buffer replacement as above; only where the kernels keep their working tables differs.)
+ * p1_msg_pack takes 12 bytes of device scratch per 2048-word tile from the library's block pool, which
+ * falls through to cudaMalloc the first time a size is asked for.  Hosts that cannot have that happen when
+ * a message is due - a provider whose own arena already holds all of the GPU's memory, the per-peer threads
+ * of --use_ot mode (an allocation waits for the whole device and so stalls every other peer's session on
+ * that GPU), a party under an operator's memory cap that might refuse the request in mid-protocol - call
+ * this instead.  It makes no cudaMalloc / cudaFree / pool request and stages nothing: the scratch is a fixed
+ * array inside libp1gpu.so's device image (P1_MSG_PACK_STATIC_MAX_TILES * 12 bytes = 768 KB, resident on
+ * every GPU that loads the library until the process exits).
+ *   - arguments, output bytes and sizes exactly as p1_msg_pack, except that `values_dev` must be a DEVICE
+ *     array (a host array would have to be staged);
+ *   - limit: count * max(1, ceil(n_words / 2048)) <= P1_MSG_PACK_STATIC_MAX_TILES, i.e. up to 134 M ring
+ *     words per call; a larger call fails with a message that says so - split the batch, or use p1_msg_pack;
+ *   - the first call on each GPU looks up the array's address on that device (cudaGetSymbolAddress, with the
+ *     context's device current) and keeps it; make that first call before starting any stream capture;
+ *   - every call on a GPU, from any context, works in the same array.  Nothing in it needs clearing between
+ *     calls (each entry is written before it is read within a call), but two calls whose kernels may run at the
+ *     same time on one GPU - different contexts, hence different streams - overwrite each other's tables and
+ *     produce garbage: order them (p1_ctx_wait) or keep to one context per GPU for this entry point;
+ *   - not covered by p1_ctx_profile (the event brackets allocate). */
+#define P1_MSG_PACK_STATIC_MAX_TILES 65536
+int p1_msg_pack_static(p1_ctx *ctx, const void *vec_dev, size_t ld_words, size_t n_words, size_t count,
+                       const uint64_t *values_dev, uint8_t *out_dev, size_t stride_bytes, uint64_t *sizes_dev);
 /* Inverse.  sizes: count uint64_t message lengths, host or device (each <= stride_bytes; the
  * whole stride must be readable).  Every message must carry exactly n_words vector elements
  * in the canonical form above (what protobuf-c emits); status_dev[p] = 0 on success, else a

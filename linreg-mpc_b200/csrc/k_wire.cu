@@ -490,6 +490,94 @@ extern "C" int p1_msg_pack(p1_ctx *ctx, const void *vec_dev, size_t ld_words, si
 	return 0;
 }
 
+// ------------------------------------------------------------------ p1_msg_pack_static: the same pack, no allocation
+//
+// p1_msg_pack needs 12 bytes of device scratch per 2048-word tile (k_pack_len's byte counts, k_pack_scan's
+// tile offsets) and takes them from the block pool, i.e. from cudaMalloc when the pool has no block of that
+// size.  Some hosts of this library cannot afford that call at the moment they send a message:
+//   - a provider process that gave all of the GPU's memory to its own arena at start-up (X, y and the message
+//     buffers of a 180 GB shard are sized once; nothing is left for the driver to hand out later);
+//   - the per-peer threads of --use_ot mode, which share one GPU: cudaMalloc and cudaFree wait for the whole
+//     device, so one thread's allocation stalls the kernels of every other peer's session;
+//   - a party run under an operator-set memory cap, where an allocation in the middle of the protocol may be
+//     refused after the peers have already been sent half of their messages.
+// For them the scratch lives in the library image itself: the array below is part of libp1gpu.so's device
+// data, so every GPU on which the library's kernels are loaded holds these 768 KB until the process exits,
+// whether this entry point is used or not.  The three kernels are the ones p1_msg_pack launches; only where
+// their tile tables live differs, so the bytes produced are the same.
+//
+// In host code `g_pack_static` is only a handle for the runtime - not an address a kernel could use.  The
+// real address differs per GPU and is looked up with cudaGetSymbolAddress the first time the entry point runs
+// on a device (with that device current), then remembered.
+static __device__ __align__(256) unsigned char g_pack_static[(size_t) P1_MSG_PACK_STATIC_MAX_TILES * 12];
+
+#define PK_STATIC_MAX_DEVICES 64
+static std::mutex g_pack_static_mu;
+static void *g_pack_static_addr[PK_STATIC_MAX_DEVICES];   // per CUDA device ordinal, NULL = not looked up yet
+
+// device address of g_pack_static on the current device (the caller has made `device` current)
+static int pack_static_addr(int device, void **addr) {
+	P1_CHECK(device >= 0 && device < PK_STATIC_MAX_DEVICES, "p1_msg_pack_static: device ordinal %d not supported (max %d)",
+		device, PK_STATIC_MAX_DEVICES - 1);
+	std::lock_guard<std::mutex> l(g_pack_static_mu);
+	if(!g_pack_static_addr[device]) {
+		void *p = NULL;
+		P1_CUDA(cudaGetSymbolAddress(&p, g_pack_static));
+		P1_CHECK(p, "p1_msg_pack_static: no device address for the scratch array on device %d", device);
+		g_pack_static_addr[device] = p;
+	}
+	*addr = g_pack_static_addr[device];
+	return 0;
+}
+
+extern "C" int p1_msg_pack_static(p1_ctx *ctx, const void *vec_dev, size_t ld_words, size_t n_words, size_t count,
+	const uint64_t *values_dev, uint8_t *out_dev, size_t stride_bytes, uint64_t *sizes_dev) {
+	P1_ENTER(ctx);
+	if(!count) return 0;
+	const size_t w = ctx->bits_p1 / 8;
+	P1_CHECK(values_dev && out_dev && sizes_dev && (vec_dev || !n_words), "p1_msg_pack_static: arguments may not be null");
+	P1_CHECK(count <= 65535, "p1_msg_pack_static: at most 65535 messages per call");
+	// size limit first: a call that is too large is refused before any pointer is looked at
+	const size_t tiles = (n_words + PK_TILE - 1) / PK_TILE;
+	const size_t ent = count * (tiles ? tiles : 1);
+	P1_CHECK(tiles <= P1_MSG_PACK_STATIC_MAX_TILES && ent <= P1_MSG_PACK_STATIC_MAX_TILES,
+		"p1_msg_pack_static: %zu messages of %zu words need %zu tile entries, the built-in scratch holds %d "
+		"(count * ceil(n_words / %d) <= %d); split the batch or use p1_msg_pack",
+		count, n_words, ent, P1_MSG_PACK_STATIC_MAX_TILES, PK_TILE, P1_MSG_PACK_STATIC_MAX_TILES);
+	P1_CHECK(stride_bytes % 16 == 0 && stride_bytes >= p1_msg_max_bytes(ctx, n_words),
+		"p1_msg_pack_static: stride of %zu bytes (need a multiple of 16, at least %zu)", stride_bytes, p1_msg_max_bytes(ctx, n_words));
+	P1_CHECK(((uintptr_t) out_dev & 15) == 0 && ((uintptr_t) vec_dev & 15) == 0 && (ld_words * w) % 16 == 0 && (count == 1 || ld_words >= n_words),
+		"p1_msg_pack_static: buffers must be 16-byte aligned and vectors at least n_words apart");
+	// p1_msg_pack stages a host `values` array through the context's copy slot; here nothing is staged
+	P1_CHECK(p1_is_device_ptr(values_dev), "p1_msg_pack_static: values must already be on the device");
+	void *ws = NULL;
+	if(pack_static_addr(ctx->device, &ws)) return 1;
+	PackParams P;
+	P.vec = vec_dev; P.ld = ld_words; P.n = n_words; P.tiles = (uint32_t) tiles;
+	P.out = out_dev; P.stride = stride_bytes; P.sizes = sizes_dev; P.values = values_dev;
+	// same split as wire_ws: offsets first, sums behind them.  Nothing has to start at zero: k_pack_len writes
+	// every tile_sum entry of this call before k_pack_scan reads it, and k_pack_scan writes every tile_off entry
+	// before k_pack_write reads it, so what an earlier call left in the array is never seen.
+	P.tile_off = (uint64_t *) ws;
+	P.tile_sum = (uint32_t *) ((char *) ws + p1_round_up(ent * 8, 256));
+	const dim3 grid((unsigned) tiles, (unsigned) count);
+	if(tiles) {
+		if(w == 8) k_pack_len<uint64_t><<<grid, WR_THREADS, 0, ctx->stream>>>(P);
+		else k_pack_len<uint32_t><<<grid, WR_THREADS, 0, ctx->stream>>>(P);
+		ctx->launches++;
+	}
+	k_pack_scan<<<(unsigned) count, WR_THREADS, 0, ctx->stream>>>(P, ctx->bits_p1);
+	ctx->launches++;
+	if(tiles) {
+		if(w == 8) k_pack_write<uint64_t><<<grid, WR_THREADS, 0, ctx->stream>>>(P);
+		else k_pack_write<uint32_t><<<grid, WR_THREADS, 0, ctx->stream>>>(P);
+		ctx->launches++;
+	}
+	const cudaError_t e = cudaGetLastError();
+	P1_CHECK(e == cudaSuccess, "p1_msg_pack_static: kernel launch: %s", cudaGetErrorString(e));
+	return 0;
+}
+
 extern "C" int p1_msg_unpack(p1_ctx *ctx, const uint8_t *in_dev, size_t stride_bytes, const uint64_t *sizes, size_t count,
 	size_t n_words, void *vec_dev, size_t ld_words, uint64_t *values_dev, int32_t *status_dev) {
 	P1_ENTER(ctx);

@@ -118,6 +118,7 @@ SIGNATURES = {
     "p1_group_finalize": (c_i, [c_vp, c_vp, c_vp, c_sz, c_sz, c_i, c_i, c_d, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
     "p1_msg_max_bytes": (c_sz, [c_vp, c_sz]),
     "p1_msg_pack": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp]),
+    "p1_msg_pack_static": (c_i, [c_vp, c_vp, c_sz, c_sz, c_sz, c_vp, c_vp, c_sz, c_vp]),
     "p1_msg_unpack": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz, c_sz, c_vp, c_sz, c_vp, c_vp]),
     "p1_share_bits": (c_i, [c_vp, c_vp, c_sz, c_vp]),
     "p1_parse_doubles": (c_i, [c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_vp, c_vp, c_sz]),
