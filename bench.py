@@ -56,6 +56,19 @@ def even_col_start(d, p):
     return [k * (d // p) for k in range(p)]  # experiments/generate_tests.py:54-61
 
 
+# the reference's own published phase-1 rows (AWS EC2 hosts of unrecorded type, one party per host,
+# experiments/results/phase1*/): different hardware, a network in between - recorded beside the measurement, never divided by
+PUBLISHED = {
+    "cfg2": {"what": "n=100000 d=100 p=3, TI masking, 64-bit", "dp_wall_s": 63.89, "ti_cpu_s": 36.47, "dp_cpu_s": 27.96,
+             "source": "BASELINE.md 1.1 (experiments/results/phase1/test_LR_100000x100_3_*)", "hardware": "published, different hardware (AWS EC2)"},
+    "cfg3": {"what": "n=1000000 d=500 p=5, 64-bit", "dp_wall_s": None, "never_run": True,
+             "masking_wall_s_extrapolated": 2.0e4, "use_ot_wall_s_extrapolated": 8.0e5,
+             "largest_run_published": "n=1000000 d=200 p=5 masking: 3552 s DP wall; n=1000000 d=50 p=5 --use_ot: 8227 s",
+             "source": "BASELINE.md 1.1, 1.3, 1.4 (plots/phase1_time.py:18,39 skips d=500 at n=1M)",
+             "hardware": "published, different hardware (AWS EC2)"},
+}
+
+
 def workload_config(name, wl, aggregation):
     return {"workload": "%s: synthetic n=%d d=%d, %d providers (vertical split), %d-bit phase 1, %s, precision %d"
                         % (name, wl["n"], wl["d"], wl["p"], wl["bits_p1"], aggregation, wl["precision"]),
@@ -229,7 +242,7 @@ def run_reference_arm(args, wl, cfg):
     per_pair = (8.0 if use_ot else 0.2) * (min(wl["n"], 1_000_000) / 1e6)
     d_s, n_s = 5, None
     for cand, pairs in ((20, 176), (10, 48)):
-        if per_pair * pairs <= budget:
+        if per_pair * pairs <= budget * 1.05:      # a tolerance: 0.2 * 48 is 9.600000000000001, the driver's budget 9.6
             d_s = cand
             break
     if use_ot and per_pair * 14 > budget:
@@ -247,7 +260,7 @@ def run_reference_arm(args, wl, cfg):
             "step_is": "one pass of the reference over the bounded sample described in cpu_baseline.sample (a rate, not the full workload)",
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": smp.threads, "kind": smp.kind, "sample": smp.describe()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "host_cores": os.cpu_count()}
+            "host_cores": os.cpu_count(), "d_sample": smp.d, "n_sample": smp.n, "cross_pairs_sample": smp.cross_pairs()}
     print(json.dumps(line))
     return 0
 
@@ -483,7 +496,8 @@ def main():
         "party_b_mask": C * 3 * nb,                                  # column + mask read, message written
         "party_a_step": C * 4 * nb,                                  # column, mask, peer message read; message written
         "party_b_share": C * 2 * nb,                                 # peer message + column read
-        "masking_fused": C * 4 * nb,                                 # columns a_i, b_j read; messages b->a, a->b written
+        "masking_fused": C * 4 * nb,                                 # SURVEY 8(d): columns a_i, b_j read; messages b->a, a->b written
+                                                                     # (a_i is shared by consecutive pairs and comes from L2: see hbm_bytes_expected)
         "gram_imad": (d + 1) * nb,                                   # every owned column read once
         "gram_limbs": limb_bytes,                                    # words read, digit planes written
         "cot_recv": cots * (16 + w),                                 # U written (16 B / OT), pads stashed
@@ -526,7 +540,16 @@ def main():
                     "avg_launch_ms": kd["avg_ms"]}
         if kd["bound"] == "hbm":
             roofline["algorithmic_bytes_per_launch"] = alg_bytes[dominant] / max(kd["launches_per_step"], 1)
+        if dominant == "masking_fused":
+            # a_i is re-used by the consecutive pairs of a launch and stays in L2, so HBM sees ~3 n w per pair
+            exp_b = C * 3 * nb / max(kd["launches_per_step"], 1)
+            roofline["hbm_bytes_expected_per_launch"] = exp_b
+            roofline["achieved_on_expected_hbm_bytes"] = exp_b / (kd["avg_ms"] * 1e-3) / 1e9
+            roofline["frac_on_expected_hbm_bytes"] = roofline["achieved_on_expected_hbm_bytes"] / kd["peak"]
+        roofline["avg_launch_ms_note"] = ("from one extra profiled step on a single pipe with event brackets around every launch "
+                                          "(p1_ctx_profile); the timed step overlaps two pipes and is about 1 % faster per launch")
         if "lsu_bound" in kd:
+            roofline["limiter"] = "lsu"
             roofline["lsu_bound"] = kd["lsu_bound"]
             roofline["note"] = ("this kernel is bound by shared-memory lookups (T-table AES), not by HBM: lsu_bound is its roofline; "
                                 "the hbm figures are the required keys")
@@ -536,8 +559,13 @@ def main():
             if tr and "lsu_bound" in roofline and tr.get("l1tex_data_stage"):
                 roofline["lsu_bound"] = dict(roofline["lsu_bound"], ncu_l1tex_data_stage=tr["l1tex_data_stage"])
             if tr and tr.get("pairs") is None:
-                roofline["traffic"] = tr["bytes_per_launch"]
-                roofline["traffic_source"] = tr["source"]
+                # a capture is evidence for the shape it was taken on only: rows, columns, providers and ring width must match
+                if (tr.get("n_rows") == n_rows and tr.get("ring_bits") == wl["bits_p1"] and tr.get("d") == d
+                        and tr.get("providers", p) == p):
+                    roofline["traffic"] = tr["bytes_per_launch"]
+                    roofline["traffic_source"] = tr["source"]
+                else:
+                    roofline["traffic_source"] = "no ncu --set full capture of %s at this shape (profiles/ncu_traffic.json holds: %s)" % (dominant, tr.get("launch"))
             elif tr and tr["n_rows"] == n_rows and tr["ring_bits"] == wl["bits_p1"]:
                 # captured for tr["pairs"] pairs per launch; the traffic is linear in the pairs of a launch
                 per_launch = C / max(kd["launches_per_step"], 1)
@@ -579,10 +607,15 @@ def main():
                         done += 1
             L1 = box.sched.kind == 1
             only = np.unique(np.concatenate([np.array(only, dtype=np.int64), box.sched.slot[L1]]))
-        check = check_run(lib, po.Oracle(), box, shares, Xd, yd, samples=16, diag_samples=4, only_slots=only)
+        # masking with the single-key stream: both providers' share words of 32 cross pairs of the TIMED schedule replayed
+        # on the CPU at their true stream positions (row shards: partial dots, ring sum over ranks)
+        check = check_run(lib, po.Oracle(), box, shares, Xd, yd, samples=16, diag_samples=4, only_slots=only,
+                          ti_key=None if (use_ot or seeded) else key, pairs_done=C, cross_samples=32)
         check["shares_nonzero"] = bool(np.any(shares))
         check["what"] = ("sum over providers of every pre-shift share word == one-provider tcgen05 Gram (all off-diagonal + share_b words), "
-                         "all diagonal words and statistics, sampled words vs the CPU oracle's ring dot / sequential double diagonal")
+                         "all diagonal words and statistics, sampled words vs the CPU oracle's ring dot / sequential double diagonal; "
+                         "sampled_cross_pair_*: both providers' masked share words of sampled cross pairs vs oracle.ti_pair + the "
+                         "party algebra at the pair's true stream offset (src/phase1.c:186-222,270-278)")
 
     # ---- the same protocol with every message through the protobuf wire format on the GPU (what separate
     # boxes execute per pair, minus the network): a bounded sample of the cross pairs, extrapolated
@@ -660,6 +693,7 @@ def main():
                 "roofline": roofline, "clocks": clocks,
                 "sustained": sustained, "int8_peak_probe": int8,
                 "e2e": e2e, "e2e_dropin": dropin, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
+        line["published"] = PUBLISHED.get(args.workload)
         if wire:
             line["value_with_wire"] = wire["value_with_wire"]
         if use_ot:

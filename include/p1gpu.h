@@ -463,7 +463,10 @@ void p1_gdata_free(p1_gdata *data);
 const p1_data *p1_gdata_shard(const p1_gdata *data, int g);
 
 /* the group's accumulators: p1_acc_len(d) words per device, zeroed by p1_group_acc_reset; every call
- * below adds into them; p1_group_reduce leaves their sum in device 0's (p1_group_acc_dev(grp, 0)) */
+ * below adds into them; p1_group_reduce leaves their sum in device 0's (p1_group_acc_dev(grp, 0)) and ZEROES
+ * the other devices' (in both reduce modes), so the sequence reduce -> more pairs -> reduce is allowed and
+ * equals one reduce at the end: no partial sum is ever counted twice.  Between a reduce and the next
+ * accumulating call, p1_group_acc_dev(grp, g >= 1) therefore reads as zeros. */
 int p1_group_acc_reset(p1_group *grp, size_t d);
 uint64_t *p1_group_acc_dev(p1_group *grp, int g);
 int p1_group_reduce(p1_group *grp);

@@ -120,16 +120,20 @@ static int group_join(p1_group *grp) {
 	return 0;
 }
 
-// dst[i] += sum over the other devices' src_g[i] (wrapping u64): P2P loads over NVLink
-__global__ void k_group_reduce(uint64_t *__restrict__ dst, uint64_t *const *__restrict__ src, int nsrc, size_t len) {
+// dst[i] += sum over the other devices' src_g[i] (wrapping u64): P2P loads over NVLink.  clear: the peers' words
+// are zeroed once they have been added (P2P stores), so that a partial sum is never counted twice
+__global__ void k_group_reduce(uint64_t *__restrict__ dst, uint64_t *const *__restrict__ src, int nsrc, size_t len, int clear) {
 	for(size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < len; i += (size_t) gridDim.x * blockDim.x) {
 		uint64_t s = dst[i];
-		for(int g = 1; g < nsrc; g++) s += src[g][i];
+		for(int g = 1; g < nsrc; g++) {
+			s += src[g][i];
+			if(clear) src[g][i] = 0;
+		}
 		dst[i] = s;
 	}
 }
 
-static int reduce_p2p(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len) {
+static int reduce_p2p(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len, bool clear = false) {
 	if(grp->ndev == 1 || !len) return 0;
 	p1_ctx *c0 = grp->ctx[0];
 	P1_CUDA(cudaSetDevice(c0->device));
@@ -138,7 +142,7 @@ static int reduce_p2p(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len) 
 	unsigned grid = (unsigned) ((len + 255) / 256);
 	if(grid > (unsigned) c0->sm_count * 4) grid = c0->sm_count * 4;
 	p1_prof_begin(c0, P1_K_MISC);
-	k_group_reduce<<<grid, 256, 0, c0->stream>>>(bufs[0], grp->peer_tab_dev, grp->ndev, len);
+	k_group_reduce<<<grid, 256, 0, c0->stream>>>(bufs[0], grp->peer_tab_dev, grp->ndev, len, clear ? 1 : 0);
 	P1_LAUNCHED(c0);
 	return 0;
 }
@@ -173,7 +177,7 @@ static int nccl_load(p1_group *grp) {
 	return 0;
 }
 
-static int reduce_nccl(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len) {
+static int reduce_nccl(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len, bool clear = false) {
 	if(grp->ndev == 1 || !len) return 0;
 	if(nccl_load(grp)) return 1;
 	const int ncclUint64 = 5, ncclSum = 0;      // nccl.h: ncclDataType_t / ncclRedOp_t
@@ -185,11 +189,16 @@ static int reduce_nccl(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len)
 		P1_CHECK(rc == 0, "ncclAllReduce failed (%d)", rc);
 	}
 	P1_CHECK(f_group_end() == 0, "ncclGroupEnd failed");
+	// the all-reduce leaves the sum everywhere; only device 0 keeps it, or the next reduce would add it ndev times
+	if(clear) for(int g = 1; g < grp->ndev; g++) {
+		P1_CUDA(cudaSetDevice(grp->ctx[g]->device));
+		P1_CUDA(cudaMemsetAsync(bufs[g], 0, len * sizeof(uint64_t), grp->ctx[g]->stream));
+	}
 	return group_join(grp);
 }
 
-static int group_reduce(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len) {
-	return grp->reduce_mode == 1 ? reduce_nccl(grp, bufs, len) : reduce_p2p(grp, bufs, len);
+static int group_reduce(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len, bool clear) {
+	return grp->reduce_mode == 1 ? reduce_nccl(grp, bufs, len, clear) : reduce_p2p(grp, bufs, len, clear);
 }
 
 // ------------------------------------------------------------------ group
@@ -334,11 +343,12 @@ extern "C" int p1_group_acc_reset(p1_group *grp, size_t d) {
 
 extern "C" uint64_t *p1_group_acc_dev(p1_group *grp, int g) { return grp && g >= 0 && g < grp->ndev ? grp->acc[g] : NULL; }
 
-// sum of the devices' partial accumulators, left in device 0's accumulator (all of them with NCCL)
+// sum of the devices' partial accumulators, left in device 0's accumulator; the other devices' accumulators are
+// zero afterwards, so accumulating further and reducing again adds only what is new (device 0 + new partials)
 extern "C" int p1_group_reduce(p1_group *grp) {
 	P1_CHECK(grp && grp->acc_len, "p1_group_reduce: no accumulator");
 	if(grp->reduced) return 0;
-	if(group_reduce(grp, grp->acc, grp->acc_len)) return 1;
+	if(group_reduce(grp, grp->acc, grp->acc_len, true)) return 1;
 	grp->reduced = true;
 	return 0;
 }

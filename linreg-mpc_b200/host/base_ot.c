@@ -18,10 +18,13 @@
  *   k_i^0 = H(i, a B_i)                              k_i^{Delta_i} = H(i, b_i A)
  *   k_i^1 = H(i, a B_i - a A)
  *
- * H = SHA-256 over a domain tag, the two party indices, i and the affine point, cut to 16 bytes.
- * Points travel as affine (x, y), 64 bytes, and are checked to lie on the curve; scalars are
- * multiples of the cofactor 8, which removes small-order components.  Field and curve arithmetic:
- * radix-2^16 limbs in int64 (constant-time selects), the textbook extended-coordinates addition law.
+ * H = SHA-256 over a domain tag, the two party indices, i, A and B_i as sent, and the affine shared point, cut to
+ * 16 bytes.  Points travel as affine (x, y), 64 bytes, and are checked to lie on the curve; an A of small order
+ * (8 A = neutral) is refused; scalars are multiples of the cofactor 8, which removes small-order components.
+ * Secrets are wiped with explicit_bzero.  SEMI-HONEST ONLY, like the reference's "honest" OT extension: nothing here
+ * defends against a peer that deviates from the protocol beyond those two point checks.
+ * Field and curve arithmetic: radix-2^16 limbs in int64 (constant-time selects), the textbook extended-coordinates
+ * addition law; the limb carry chain follows TweetNaCl's car25519 (public domain), as does the 16-limb layout.
  */
 #define _POSIX_C_SOURCE 201605L
 #define _DEFAULT_SOURCE
@@ -286,14 +289,34 @@ static int random_scalar(uint8_t s[32]) {
 	return 0;
 }
 
-static void seed_of(uint8_t seed[16], int sender_party, int receiver_party, int i, const ge *p) {
-	uint8_t msg[16 + 12 + 64], dig[32];
-	memcpy(msg, "p1gpu-base-ot-v1", 16);
+/* the key of OT i: bound to the session (tag, parties, i) and to the transcript (A and B_i as they travelled), so
+ * that a key is tied to the messages that produced it and not to the shared point alone */
+static void seed_of(uint8_t seed[16], int sender_party, int receiver_party, int i, const uint8_t A_wire[64],
+	const uint8_t B_wire[64], const ge *p) {
+	uint8_t msg[16 + 12 + 3 * 64], dig[32];
+	memcpy(msg, "p1gpu-base-ot-v2", 16);
 	const uint32_t v[3] = {(uint32_t) sender_party, (uint32_t) receiver_party, (uint32_t) i};
 	for(int k = 0; k < 3; k++) for(int b = 0; b < 4; b++) msg[16 + 4 * k + b] = (uint8_t) (v[k] >> (8 * b));
-	ge_to_bytes(msg + 28, p);
+	memcpy(msg + 28, A_wire, 64);
+	memcpy(msg + 92, B_wire, 64);
+	ge_to_bytes(msg + 156, p);
 	p1host_sha256(msg, sizeof(msg), dig);
 	memcpy(seed, dig, 16);
+	explicit_bzero(msg, sizeof(msg));
+	explicit_bzero(dig, sizeof(dig));
+}
+
+/* 1 if 8 P is the neutral element (0, 1): P lies in the small-order subgroup, and a scalar that is a multiple of
+ * the cofactor would send it to the neutral element - every key derived from it would be public */
+static int ge_small_order(const ge *p) {
+	static const uint8_t eight[32] = {8};
+	uint8_t enc[64];
+	ge r;
+	ge_scalarmult(&r, p, eight);
+	ge_to_bytes(enc, &r);
+	int nz = enc[32] ^ 1;
+	for(int k = 0; k < 64; k++) if(k != 32) nz |= enc[k];
+	return nz == 0;
 }
 
 /* role, seeds0, seeds1, delta as for p1host_base_ot (phase1_gpu.c): role 1 = extension sender */
@@ -319,11 +342,14 @@ int p1host_base_ot_co15(ProtocolDesc *pd, int sender_party, int receiver_party, 
 			ge_scalarmult(&P0, &B, a);
 			P1 = P0;
 			ge_add(&P1, &aA);                     /* a B - a A */
-			seed_of(seeds0[i], sender_party, receiver_party, i, &P0);
-			seed_of(seeds1[i], sender_party, receiver_party, i, &P1);
+			seed_of(seeds0[i], sender_party, receiver_party, i, wire, all + 64 * i, &P0);
+			seed_of(seeds1[i], sender_party, receiver_party, i, wire, all + 64 * i, &P1);
 		}
 		memset(delta, 0, 16);
-		memset(a, 0, sizeof(a));
+		explicit_bzero(a, sizeof(a));
+		explicit_bzero(&aA, sizeof(aA));
+		explicit_bzero(&P0, sizeof(P0));
+		explicit_bzero(&P1, sizeof(P1));
 	} else {
 		/* extension sender = base-OT receiver with the choice string Delta */
 		uint8_t b[32];
@@ -331,6 +357,7 @@ int p1host_base_ot_co15(ProtocolDesc *pd, int sender_party, int receiver_party, 
 		if(getrandom(delta, 16, 0) != 16) { fprintf(stderr, "p1host_base_ot: getrandom failed\n"); return 1; }
 		if(orecv(pd, 0, wire, 64) != 64) return 1;
 		if(ge_from_bytes(&A, wire)) { fprintf(stderr, "p1host_base_ot: peer sent a point that is not on the curve\n"); return 1; }
+		if(ge_small_order(&A)) { fprintf(stderr, "p1host_base_ot: peer sent a point of small order\n"); return 1; }
 		for(int i = 0; i < 128; i++) {
 			const int bit = (delta[i / 8] >> (i % 8)) & 1;
 			if(random_scalar(b)) { fprintf(stderr, "p1host_base_ot: getrandom failed\n"); return 1; }
@@ -341,12 +368,15 @@ int p1host_base_ot_co15(ProtocolDesc *pd, int sender_party, int receiver_party, 
 			ge_cswap(&B, &sum, bit);
 			ge_to_bytes(all + 64 * i, &B);
 			ge_scalarmult(&K, &A, b);
-			seed_of(seeds0[i], sender_party, receiver_party, i, &K);
+			seed_of(seeds0[i], sender_party, receiver_party, i, wire, all + 64 * i, &K);
+			explicit_bzero(&sum, sizeof(sum));
 		}
 		if(osend(pd, 0, all, sizeof(all)) < 0) return 1;
 		orecv(pd, 0, NULL, 0);
 		memset(seeds1, 0, 128 * 16);
-		memset(b, 0, sizeof(b));
+		explicit_bzero(b, sizeof(b));
+		explicit_bzero(&K, sizeof(K));
+		explicit_bzero(&B, sizeof(B));
 	}
 	return 0;
 }

@@ -226,9 +226,12 @@ def test_cfg5_as_written(p1lib, oracle):
     shares = box.run_masking(X, y, po.TI_KEY)
     assert box.sched.num_cross == 475_950
     assert int(shares.max()) < 2 ** 32
-    res = check_run(p1lib, oracle, box, shares, X, y, samples=24, diag_samples=6)
+    res = check_run(p1lib, oracle, box, shares, X, y, samples=24, diag_samples=6, ti_key=po.TI_KEY, cross_samples=24)
     box.close()
     assert res["ok"] and res["words_checked"] == 500_500 and res["downconvert_all_words"], res
+    # both providers' masked words of 24 cross pairs, up to q = 475 949 (110 multiples of 2^32 keystream blocks in)
+    assert res["sampled_cross_pairs"] == 24 and res["sampled_cross_pair_words_match"], res
+    assert max(res["sampled_cross_pair_2p32_block_epochs"]) == 110, res
 
 
 def test_cfg4_as_written(p1lib, oracle):
@@ -257,6 +260,6 @@ def test_cfg4_as_written(p1lib, oracle):
     assert np.array_equal(res[0], res[1])
     box = phase1.Phase1Box(p1lib, n, d, po.even_col_start(d, 5), 30, 0, 32, 32, batch_pairs=24)
     shares = box.run_masking(X, y, po.TI_KEY)
-    out = check_run(p1lib, oracle, box, shares, X, y, samples=8, diag_samples=2)
+    out = check_run(p1lib, oracle, box, shares, X, y, samples=8, diag_samples=2, ti_key=po.TI_KEY, cross_samples=10)
     box.close()
-    assert out["ok"], out
+    assert out["ok"] and out["sampled_cross_pair_words_match"] and out["sampled_cross_pairs"] == 10, out

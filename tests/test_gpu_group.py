@@ -94,6 +94,39 @@ def test_group_encode_local_block_finalize(p1lib, oracle, devs, b1, b2, prec, pr
 
 
 @pytest.mark.parametrize("devs", _device_lists())
+@pytest.mark.parametrize("nccl", [False, True])
+def test_group_reduce_twice_counts_every_partial_once(p1lib, devs, nccl):
+    """reduce -> more pairs -> reduce == one reduce at the end (include/p1gpu.h, p1_group_reduce): the
+    peers' partial sums are cleared once they have been added, in both reduce modes; a reduce with nothing
+    new in between changes nothing"""
+    lib = p1lib
+    if nccl and len(set(devs)) != len(devs):
+        pytest.skip("NCCL needs distinct devices")
+    n, d = 4000 + 13, 12
+    X, y, _ = po.generate_lin_regression(n, d, seed=33)
+    nz = float(np.sqrt(2.0 ** 56 * n))
+    res = []
+    for split in (False, True):
+        grp = mkgroup(lib, devs, 64, 64, nccl)
+        gd = c_vp()
+        lib.check(lib.p1_group_encode(grp, vp(X), vp(y), n, d, nz, 56, ctypes.byref(gd)))
+        lib.check(lib.p1_group_acc_reset(grp, d))
+        lib.check(lib.p1_group_local_block(grp, gd, 0, 5, 0, 0))
+        if split:
+            first = group_acc_sum(lib, grp, d).copy()
+            assert np.array_equal(group_acc_sum(lib, grp, d), first)     # nothing new: unchanged
+            for g in range(1, len(devs)):                                 # the peers start again from zero
+                L = int(lib.p1_acc_len(d))
+                assert not d2h(lib, lib.p1_group_ctx(grp, g), lib.p1_group_acc_dev(grp, g), L, np.uint64).any()
+        lib.check(lib.p1_group_local_block(grp, gd, 5, d, 1, 0))
+        res.append(group_acc_sum(lib, grp, d).copy())
+        lib.p1_gdata_free(gd)
+        lib.p1_group_destroy(grp)
+    assert res[0].any()
+    assert np.array_equal(res[0], res[1])
+
+
+@pytest.mark.parametrize("devs", _device_lists())
 def test_group_sequential_diagonal_chain(p1lib, oracle, devs):
     """words >= 2^26 defeat the exact diagonal shortcut: the literal double loop (src/phase1.c:563-566) is
     chained over the slabs in device order and must equal the oracle's single sequential pass"""

@@ -11,6 +11,11 @@ At BASELINE sizes the CPU oracle cannot replay every word (hours), so a run is c
   3. sampled words of that Gram against the CPU oracle (`oracle.dot`, `oracle.diag`, i.e.
      src/phase1.c:14-20 and :562-567) on columns read back from the device, rank slices combined
      with the ring sum (dot) or gathered in rank order (the sequential double diagonal);
+  3b. sampled CROSS pairs, both providers' masked share words against the CPU oracle at the pair's true
+     position q of the TI stream (`oracle.ti_pair`, src/phase1.c:270-278): share_a = <b_j + x, y> - (<x,y> - r)
+     (:186-196) in the accumulator of i's owner, share_b = <a_i - y, b_j> - r (:201-222) in j's; the sum invariant
+     of 1. cannot see a wrong mask (it cancels between the two parties), these words can.  The sample holds
+     q = 0, the last pair and the pairs around the first and the last multiple of 2^32 keystream blocks;
   4. the 64 -> 32 hand-off (src/phase1.c:609-620,629-635) on every word against
      `oracle.downconvert` when the configuration has one.
 The product path never imports this file.
@@ -59,17 +64,73 @@ def _gather_rows(col, per, group, dev):
     return out.cpu().numpy().view(col.dtype)
 
 
-def check_run(lib, oracle, box, shares, X, y, samples=16, diag_samples=4, seed=11, only_slots=None):
+def sample_cross_pairs(C, n_total, bits, count, rng):
+    """pair numbers q to replay: both ends, the pairs around the first and the last crossing of a multiple of 2^32
+    AES blocks of the TI stream (pair q starts at word q * (2 n + 1)), the rest drawn uniformly"""
+    if C <= count:
+        return list(range(C))
+    words_per_block = 128 // bits
+    picks = {0, 1, C - 2, C - 1}
+    per_pair = 2 * n_total + 1
+    last_block = (C * per_pair) // words_per_block
+    for m in sorted({1, last_block >> 32} - {0}):
+        qx = (m << 32) * words_per_block // per_pair             # the pair that holds block m * 2^32
+        picks |= {q for q in (qx - 1, qx, qx + 1) if 0 <= q < C}
+    while len(picks) < count:
+        picks.add(int(rng.integers(0, C)))
+    return sorted(picks)
+
+
+def check_cross_pairs(lib, oracle, box, acc, ti_key, pairs_done=None, count=16, seed=12):
+    """3b of the module text.  acc: box.accumulators() (combined over ranks, values applied).  Collective over box.group."""
+    S, d, bits = box.sched, box.d, box.bits_p1
+    mask = np.uint64((1 << bits) - 1)
+    C = S.num_cross if pairs_done is None else min(S.num_cross, int(pairs_done))
+    if not C:
+        return {"sampled_cross_pairs": 0}
+    qs = sample_cross_pairs(C, box.n_total, bits, count, np.random.default_rng(seed))
+    ctx = box.ctxs[0]
+    cols = {}
+    col = lambda c: cols.setdefault(int(c), column(lib, ctx, box.data, int(c), box.n_rows, bits))
+    rows = slice(box.row0, box.row0 + box.n_rows)
+    partial, vals, got = [], [], []
+    with np.errstate(over="ignore"):
+        for q in qs:
+            t = S.cross[q]
+            i, j = int(S.i[t]), int(S.j[t])
+            x, y, va, vb = oracle.ti_pair(ti_key, q, box.n_total, bits)        # the whole vectors at the pair's offset
+            x, y = x[rows], y[rows]
+            a_i, b_j = col(i), col(j)
+            partial.append(oracle.dot(b_j + x, y, bits))                         # party a: <b_j + x, y>
+            partial.append(oracle.dot(a_i - y, b_j, bits))                       # party b: <a_i - y, b_j>
+            vals += [va, vb]
+            slot = int(S.slot[t])
+            got += [acc[int(S.owner_i[t]), slot], acc[int(S.owner_j[t]), slot]]
+        dots = _ring_sum_over_ranks(np.array(partial, dtype=np.uint64), box.group, box.dev)
+        want = (dots - np.array(vals, dtype=np.uint64)) & mask
+    got = np.array(got, dtype=np.uint64) & mask
+    blocks = [q * (2 * box.n_total + 1) * bits // 128 >> 32 for q in qs]
+    return {"sampled_cross_pairs": len(qs), "sampled_cross_pair_words": 2 * len(qs),
+            "sampled_cross_pair_words_match": bool(np.array_equal(got, want)),
+            "sampled_cross_pair_q": [int(q) for q in qs],
+            "sampled_cross_pair_2p32_block_epochs": sorted(set(int(b) for b in blocks))}
+
+
+def check_run(lib, oracle, box, shares, X, y, samples=16, diag_samples=4, seed=11, only_slots=None,
+              ti_key=None, pairs_done=None, cross_samples=16):
     """`box`: the Phase1Box that produced `shares` (its accumulators and column store are still
     alive); X, y: the rank's rows as given to box.encode.  Collective over box.group: every rank
     must call it.  only_slots: restrict the sum invariant to these accumulator slots (a run that executed
-    only part of the cross-pair schedule).  Returns a dict of booleans / counts (meaningful on every rank)."""
+    only part of the cross-pair schedule).  ti_key: the TI key of a masking run with the single-key stream (not seeded
+    masks): both providers' words of `cross_samples` cross pairs (among the first pairs_done, default all) are replayed on
+    the CPU.  Returns a dict of booleans / counts (meaningful on every rank)."""
     from linreg_mpc_b200 import phase1
     S, d, nA = box.sched, box.d, box.sched.nA
     bits, bits2 = box.bits_p1, box.bits_p2
     mask = np.uint64((1 << bits) - 1)
     group, dev = box.group, box.dev
     acc = box.accumulators()                         # [num_dp, acc_len] u64, combined over ranks, values applied
+    cross = check_cross_pairs(lib, oracle, box, acc, ti_key, pairs_done, cross_samples, seed + 1) if ti_key is not None else {}
     # ---- the independent path: one provider, tcgen05 Gram over all d (+ target) columns
     one = phase1.Phase1Box(lib, box.n_total, d, [0], box.precision, box.precision_p2, bits, bits2, device=box.device,
                            row0=box.row0, n_rows=box.n_rows, pipes=1, gram_algo=phase1.ffi.P1_GRAM_TCGEN05, group=group)
@@ -143,5 +204,6 @@ def check_run(lib, oracle, box, shares, X, y, samples=16, diag_samples=4, seed=1
     out["sampled_diagonals"] = int(min(diag_samples, d))
     out["sampled_diagonals_match"] = bool(okd)
     one.close()
+    out.update(cross)
     out["ok"] = all(v for k, v in out.items() if isinstance(v, bool))
     return out
