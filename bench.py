@@ -287,7 +287,8 @@ def main():
     ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in host file vs reference phase1.c timing (n=1M, d=10, 3 providers)")
     ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (p1_ctx_set_option), repeatable")
     ap.add_argument("--wire-sample", type=int, default=3300, help="cross pairs to time with GPU (de)serialisation of every message (0 = skip)")
-    ap.add_argument("--ot-sample", type=int, default=8, help="masking workloads: inner products of the --use_ot path to time as a side figure (0 = skip)")
+    ap.add_argument("--gram-p1", type=int, default=1, help="1: also time the one-provider tcgen05 Gram of the instance (gram_p1 block); 0: skip")
+    ap.add_argument("--ot-sample", type=int, default=250, help="masking workloads: inner products PER GPU of the --use_ot schedule timed as the ot_workload block (0 = skip)")
     ap.add_argument("--min-sampled-s", type=float, default=2.0, help="short steps are repeated for at least this long under the clock sampler")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -637,19 +638,94 @@ def main():
                 "(src/phase1.c:100-145): what parties on separate boxes execute, minus the network; the headline step keeps all "
                 "parties on one device and hands messages over in HBM"}
 
-    # ---- --use_ot as a side figure of the masking workloads (the OT workload itself: --aggregation ot)
+    # ---- BASELINE config 3 as written (--use_ot) inside the default line, at every N: the reference's OT schedule
+    # (src/phase1.c:386-449) over enough inner products that session set-up is a small, separately reported share; the
+    # whole workload is the same loop 100 400 times (--aggregation ot runs it as the step itself)
     ot = None
     if args.ot_sample > 0 and C_all and not use_ot:
-        def ot_step():
-            box.cross_pairs_ot(ot_key, max_pairs=args.ot_sample)
-        ot_step()
-        ms_ot, _ = timed(ot_step, 2)
-        c_s = args.ot_sample * n * wl["bits_p1"]
-        rate = c_s / (ms_ot * 1e-3)
+        P_ot = min(C_all, args.ot_sample * world)         # strong scaling: rows shrink with N, so the pair count grows with it
+        box.cross_pairs_ot(ot_key, max_pairs=min(P_ot, 2 * args.pipes))    # warm-up: buffers, pads, both kernels
+        box.reset()
+        box.encode(Xd, yd)
+        box.local_blocks()
+        ms_ot, wall_ot = timed(lambda: box.cross_pairs_ot(ot_key, max_pairs=P_ot), 1)
+        setup = torch.tensor([box.ot_setup_s * 1e3], dtype=torch.float64, device=dev)
+        if group is not None:
+            dist.all_reduce(setup, op=dist.ReduceOp.MAX)
+        setup_ms = float(setup[0])
+        box.all_reduce()
+        ot_shares = box.finalize()
+        c_s = P_ot * n * wl["bits_p1"]
         total_cots = C_all * n * wl["bits_p1"]
-        ot = {"inner_products": args.ot_sample, "cots": c_s, "ms": ms_ot, "cot_per_s": rate,
-              "wire_bytes_per_cot": 16 + w, "all_cross_pairs_cots": total_cots, "all_cross_pairs_seconds_extrapolated": total_cots / rate,
-              "note": "session setup included; see --aggregation ot for the workload, its kernel table and its scaling"}
+        rate = c_s / (max(ms_ot - setup_ms, 1e-3) * 1e-3)
+        ot = {"inner_products": P_ot, "sessions": box.ot_sessions, "cots": c_s, "ms": ms_ot, "wall_ms": wall_ot,
+              "session_setup_ms": setup_ms, "session_setup_frac": setup_ms / ms_ot,
+              "cot_per_s": rate, "cot_per_s_incl_setup": c_s / (ms_ot * 1e-3), "s_per_1000_pairs": (ms_ot - setup_ms) / P_ot,
+              "wire_bytes_per_cot": 16 + w, "workload_cots": total_cots,
+              "workload_sessions": p * (p - 1) // 2,
+              "workload_seconds_extrapolated": total_cots / rate + p * (p - 1) // 2 * setup_ms * 1e-3 / max(box.ot_sessions, 1),
+              "published": PUBLISHED.get(args.workload, {}).get("use_ot_wall_s_extrapolated") if PUBLISHED.get(args.workload) else None,
+              "note": "device-timed (CUDA events on the main stream, max over ranks) over the first %d inner products of the reference's OT "
+                      "schedule; session_setup_ms = host time of derive_cot_session + p1_cot_*_new + p1_cot_free (max over ranks), reported apart "
+                      "and excluded from cot_per_s; base OTs are inputs (host/base_ot.c in the drop-in)" % P_ot}
+        if not args.no_check:
+            from oracle import pyoracle as po
+            from tools.parity_check import check_run
+            done, only = 0, []
+            for ps_, pr_, items in box.ot_schedule():
+                for (_, _, slot) in items:
+                    if done < P_ot:
+                        only.append(slot)
+                        done += 1
+            only = np.unique(np.concatenate([np.array(only, dtype=np.int64), box.sched.slot[box.sched.kind == 1]]))
+            ck = check_run(lib, po.Oracle(), box, ot_shares, Xd, yd, samples=4, diag_samples=1, only_slots=only)
+            ot["check"] = {k: ck[k] for k in ("words_checked", "sum_invariant_all_words", "all_diagonals_match", "ok")}
+            ot["check"]["what"] = ("the two providers' OT shares of every executed inner product sum to the plain ring Gram word (+ all local words); "
+                                   "share words of whole --use_ot runs are compared with the reference word for word in tests/test_gpu_fullsize.py at n = 100 000")
+
+    # ---- the one-provider Gram of this instance (the p = 1 full-Gram figure; north_star: >= 60 % of the dense
+    # int8 tensor peak): one provider owning all d + 1 columns, tcgen05 kernel forced, the kernel's own launch time from event
+    # brackets - alone (first launch after a sync) and back to back (5 launches in a row)
+    gram_p1 = None
+    if args.gram_p1 and not use_ot and d >= 16:
+        one = Phase1Box(lib, n, d, [0], wl["precision"], wl["precision_p2"], wl["bits_p1"], wl["bits_p2"], device=local,
+                        row0=row0, n_rows=n_rows, pipes=1, gram_algo=pkg.ffi.P1_GRAM_TCGEN05, group=group)
+        one.reset()
+        one.encode(Xd, yd)
+        one.local_blocks()
+        one.sync()
+        Lk = ctypes.c_int(0)
+        lib.check(lib.p1_gram_digits(one.ctxs[0], one.data, 0, d, 1, ctypes.byref(Lk)))
+        m1 = d + 1
+        ops1 = 2.0 * Lk.value ** 2 * n_rows * (m1 * (m1 - 1) // 2)
+
+        def gram_launch_ms(reps):
+            lib.check(lib.p1_ctx_profile(one.ctxs[0], 1))
+            barrier()
+            for _ in range(reps):
+                one.local_blocks()
+            one.sync()
+            ms, nl = ctypes.c_double(), ctypes.c_uint64()
+            lib.check(lib.p1_ctx_profile_read(one.ctxs[0], pkg.ffi.P1_K_GRAM_TC, ctypes.byref(ms), ctypes.byref(nl)))
+            lib.check(lib.p1_ctx_profile(one.ctxs[0], 0))
+            return ms.value, nl.value
+        ms_a, nl_a = gram_launch_ms(1)
+        ms_b, nl_b = gram_launch_ms(5)
+        v = torch.tensor([ms_a / max(nl_a, 1), (ms_b - ms_a) / max(nl_b - nl_a, 1)], dtype=torch.float64, device=dev)
+        if group is not None:
+            dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        alone, b2b = float(v[0]), float(v[1])
+        one.close()
+        gram_p1 = {"columns": m1, "rows_per_rank": n_rows, "digits": Lk.value, "int8_ops_per_launch_per_rank": ops1,
+                   "ms_alone": alone, "ms_back_to_back": b2b}
+        for tag, ms_ in (("alone", alone), ("back_to_back", b2b)):
+            tops = ops1 / (ms_ * 1e-3) / 1e12
+            gram_p1[tag] = {"tops_int8_credited_per_gpu": tops, "frac_of_measured_int8_peak": tops / int8_peak,
+                            "frac_of_nominal_dense_int8": tops / int8_nominal,
+                            "ring_gmacs_all_gpus": world * n_rows * (m1 * (m1 - 1) // 2) / (ms_ * 1e-3) / 1e9}
+        gram_p1["note"] = ("credited = 2 L^2 int8 ops per WANTED ring MAC (lower triangle only, no padding); the kernel also computes the upper "
+                           "halves of the diagonal tiles and the 501 -> 512 padding, which is why a tensor pipe that ncu shows 92 %% active credits less; "
+                           "measured peak %.0f TOP/s (p1_probe_tensor_i8 in this run), nominal 4500" % int8_peak)
 
     # ---- CPU baseline (rank 0, N = 1 only): the reference's own phase-1 code on a bounded sample
     cpu = None
@@ -692,7 +768,7 @@ def main():
                                 "event overhead included); the timed steps run %d pipes" % (ms_prof, args.pipes),
                 "roofline": roofline, "clocks": clocks,
                 "sustained": sustained, "int8_peak_probe": int8,
-                "e2e": e2e, "e2e_dropin": dropin, "wire_format_sample": wire, "use_ot_sample": ot, "cpu_baseline": cpu, "check": check}
+                "e2e": e2e, "e2e_dropin": dropin, "wire_format_sample": wire, "ot_workload": ot, "gram_p1": gram_p1, "cpu_baseline": cpu, "check": check}
         line["published"] = PUBLISHED.get(args.workload)
         if wire:
             line["value_with_wire"] = wire["value_with_wire"]

@@ -102,9 +102,12 @@ const char *p1_kernel_class_name(int kernel_class);
  *                            and leaves it off (default 0).  Results are identical either way. */
 int p1_ctx_set_option(p1_ctx *ctx, const char *name, long value);
 
-/* p1_dev_free / p1_host_free keep the block for the next request of the same size (up to 4 GB per device and
- * 4 GB of page-locked memory per process): a party that serves run after run asks for the same buffers again.
- * p1_pool_trim returns everything that is kept to the driver. */
+/* p1_dev_free / p1_host_free keep the block for the next request of the same size (up to P1GPU_POOL_MAX_MB, default
+ * 8192, MB per device and as much page-locked memory per process; environment, read once; 0 = keep nothing): a party
+ * that serves run after run asks for the same buffers again.  Blocks are zeroed before they are kept or released
+ * (P1GPU_POOL_SCRUB: 1 = device blocks and page-locked blocks up to 1 MB, the default; 2 = page-locked blocks of any
+ * size too; 0 = off), and so are the round keys and pads of a p1_cot session when it is freed.  p1_dev_free waits for
+ * the whole device, as cudaFree does.  p1_pool_trim returns everything that is kept to the driver. */
 int p1_dev_alloc(p1_ctx *ctx, size_t bytes, void **dev);
 int p1_dev_free(p1_ctx *ctx, void *dev);
 void p1_pool_trim(void);

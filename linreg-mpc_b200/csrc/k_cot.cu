@@ -316,8 +316,8 @@ extern "C" void p1_cot_free(p1_cot *s) {
 	if(!s) return;
 	cudaSetDevice(s->device);
 	cudaDeviceSynchronize();
-	p1_pool_dev_give(s->device, s->keys_dev, s->keys_bytes);
-	p1_pool_dev_give(s->device, s->pads, s->pads_bytes);
+	p1_pool_dev_give_secret(s->device, s->keys_dev, s->keys_bytes);    // expanded round keys of the base-OT seeds
+	p1_pool_dev_give_secret(s->device, s->pads, s->pads_bytes);        // hashed pads H(t) of the last inner product
 	delete s;
 }
 
@@ -357,7 +357,7 @@ static int cot_launch(p1_ctx *ctx, p1_cot *s, const p1_data *data, int32_t col, 
 		if(s->pads_bytes < need) {
 			if(s->pads) {
 				P1_CUDA(cudaDeviceSynchronize());
-				p1_pool_dev_give(s->device, s->pads, s->pads_bytes);
+				p1_pool_dev_give_secret(s->device, s->pads, s->pads_bytes);
 				s->pads_bytes = 0;
 			}
 			s->pads = p1_pool_dev_take(s->device, need);

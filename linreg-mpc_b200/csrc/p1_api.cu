@@ -50,7 +50,29 @@ int p1_small_to_dev(p1_ctx *ctx, const void *src, size_t bytes, size_t slot, con
 // Freed blocks are kept for the next request of the same size (device: per device; host: page-locked), up to
 // P1_POOL_MAX bytes each: a party that serves one run after another - and every test - asks for the same
 // buffers again, and cudaHostAlloc / cudaMalloc / cudaFree cost milliseconds per 100 MB and synchronise the device.
-#define P1_POOL_MAX ((size_t) 8 << 30)
+// Caps and scrubbing are process-wide settings read once from the environment:
+//   P1GPU_POOL_MAX_MB  bytes kept per device and of page-locked memory, in MB (default 8192; 0 = keep nothing, every
+//                      free goes back to the driver)
+//   P1GPU_POOL_SCRUB   1 (default): device blocks are zeroed before they are kept or released - OT round keys, pads,
+//                      TI masks and whatever a caller's p1_dev_alloc block held do not outlive their owner - and so are
+//                      page-locked blocks of up to 1 MB (keys and values of seeded-mask messages); 2: page-locked blocks
+//                      of any size as well (a host memset of the whole wire buffer per free); 0: nothing is zeroed
+static size_t pool_env(const char *name, size_t dflt) {
+	const char *v = getenv(name);
+	if(!v || !*v) return dflt;
+	char *end = NULL;
+	const unsigned long long x = strtoull(v, &end, 10);
+	return end && *end == 0 ? (size_t) x : dflt;
+}
+static size_t pool_max_bytes() {
+	static const size_t v = pool_env("P1GPU_POOL_MAX_MB", 8192) << 20;
+	return v;
+}
+static int pool_scrub_level() {
+	static const int v = (int) pool_env("P1GPU_POOL_SCRUB", 1);
+	return v;
+}
+#define P1_POOL_MAX pool_max_bytes()
 struct BlockPool {
 	std::mutex mu;
 	std::multimap<size_t, void *> blocks;
@@ -127,6 +149,15 @@ void p1_pool_dev_give(int device, void *p, size_t bytes) {
 	if(!p) return;
 	if(!bytes) bytes = 1;
 	if(!g_dev_pool[device & 63].give(bytes, p)) cudaFree(p);
+}
+// the same for a block that held key, pad or mask material: zeroed first (device `device` is current and idle, as for
+// p1_pool_dev_give; the memset runs on the legacy stream and is waited for, so the next owner on any stream sees zeros)
+void p1_pool_dev_give_secret(int device, void *p, size_t bytes) {
+	if(!p) return;
+	if(pool_scrub_level() >= 1 && bytes) {
+		if(cudaMemset(p, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) cudaGetLastError();
+	}
+	p1_pool_dev_give(device, p, bytes);
 }
 void *p1_pool_host_take(size_t bytes) {
 	if(!bytes) bytes = 1;
@@ -361,7 +392,7 @@ extern "C" int p1_dev_free(p1_ctx *ctx, void *dev) {
 	if(!dev) return 0;
 	P1_CUDA(cudaDeviceSynchronize());           // as cudaFree would: no stream of the device still uses the block
 	const size_t bytes = block_size_take(dev);
-	if(bytes) p1_pool_dev_give(ctx->device, dev, bytes);
+	if(bytes) p1_pool_dev_give_secret(ctx->device, dev, bytes);    // callers keep masks and messages in these blocks
 	else P1_CUDA(cudaFree(dev));
 	return 0;
 }
@@ -385,6 +416,10 @@ extern "C" int p1_host_free(p1_ctx *ctx, void *host) {
 	P1_ENTER(ctx);
 	if(!host) return 0;
 	const size_t bytes = block_size_take(host);
+	if(bytes && (pool_scrub_level() >= 2 || (pool_scrub_level() == 1 && bytes <= ((size_t) 1 << 20)))) {
+		P1_CUDA(cudaStreamSynchronize(ctx->stream));              // no copy of this context still targets the block
+		memset(host, 0, bytes);
+	}
 	if(bytes) p1_pool_host_give(host, bytes);
 	else P1_CUDA(cudaFreeHost(host));
 	return 0;

@@ -50,6 +50,7 @@ struct p1_ctx {
 // uses the block (it synchronised, as a cudaFree would have)
 void *p1_pool_dev_take(int device, size_t bytes);
 void p1_pool_dev_give(int device, void *p, size_t bytes);
+void p1_pool_dev_give_secret(int device, void *p, size_t bytes);   // zeroed first (P1GPU_POOL_SCRUB, p1_api.cu)
 void *p1_pool_host_take(size_t bytes);
 void p1_pool_host_give(void *p, size_t bytes);
 

@@ -133,16 +133,25 @@ __global__ void k_group_reduce(uint64_t *__restrict__ dst, uint64_t *const *__re
 	}
 }
 
-static int reduce_p2p(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len, bool clear = false) {
+// The kernel reads the peers' addresses (entries 1..ndev-1) from a table on device 0.  The two tables - accumulators
+// in slot 0, <x,y> partials in slot 1 - are written when those buffers are allocated (stage_peer_table, a blocking
+// copy right after the cudaMalloc), so a reduce itself moves nothing from the host and needs no host round trip.
+#define PEER_TAB_STRIDE 64
+static int stage_peer_table(p1_group *grp, int slot, const std::vector<uint64_t *> &bufs) {
+	P1_CUDA(cudaSetDevice(grp->ctx[0]->device));
+	P1_CUDA(cudaStreamSynchronize(grp->ctx[0]->stream));      // no reduce that reads the old table is still running
+	P1_CUDA(cudaMemcpy(grp->peer_tab_dev + slot * PEER_TAB_STRIDE, bufs.data(), grp->ndev * sizeof(uint64_t *), cudaMemcpyHostToDevice));
+	return 0;
+}
+
+static int reduce_p2p(p1_group *grp, int slot, uint64_t *dst, size_t len, bool clear = false) {
 	if(grp->ndev == 1 || !len) return 0;
 	p1_ctx *c0 = grp->ctx[0];
 	P1_CUDA(cudaSetDevice(c0->device));
-	// the pointer table travels through the pinned slot of context 0 (stream ordered)
-	P1_CUDA(cudaMemcpyAsync(grp->peer_tab_dev, bufs.data(), grp->ndev * sizeof(uint64_t *), cudaMemcpyHostToDevice, c0->stream));
 	unsigned grid = (unsigned) ((len + 255) / 256);
 	if(grid > (unsigned) c0->sm_count * 4) grid = c0->sm_count * 4;
 	p1_prof_begin(c0, P1_K_MISC);
-	k_group_reduce<<<grid, 256, 0, c0->stream>>>(bufs[0], grp->peer_tab_dev, grp->ndev, len, clear ? 1 : 0);
+	k_group_reduce<<<grid, 256, 0, c0->stream>>>(dst, grp->peer_tab_dev + slot * PEER_TAB_STRIDE, grp->ndev, len, clear ? 1 : 0);
 	P1_LAUNCHED(c0);
 	return 0;
 }
@@ -198,7 +207,7 @@ static int reduce_nccl(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len,
 }
 
 static int group_reduce(p1_group *grp, std::vector<uint64_t *> &bufs, size_t len, bool clear) {
-	return grp->reduce_mode == 1 ? reduce_nccl(grp, bufs, len, clear) : reduce_p2p(grp, bufs, len, clear);
+	return grp->reduce_mode == 1 ? reduce_nccl(grp, bufs, len, clear) : reduce_p2p(grp, 0, bufs[0], len, clear);   // only called on grp->acc
 }
 
 // ------------------------------------------------------------------ group
@@ -257,7 +266,7 @@ extern "C" int p1_group_create(const int *devices, int ndev, int ring_bits_p1, i
 	}
 	cudaSetDevice(devices[0]);
 	if(cudaEventCreateWithFlags(&grp->ev_main, cudaEventDisableTiming) != cudaSuccess ||
-	   cudaMalloc(&grp->peer_tab_dev, 64 * sizeof(uint64_t *)) != cudaSuccess) { p1_group_destroy(grp); return p1_fail("p1_group_create: out of memory"); }
+	   cudaMalloc(&grp->peer_tab_dev, 2 * PEER_TAB_STRIDE * sizeof(uint64_t *)) != cudaSuccess) { p1_group_destroy(grp); return p1_fail("p1_group_create: out of memory"); }
 	*out = grp;
 	return 0;
 }
@@ -311,7 +320,7 @@ static int ensure_acc(p1_group *grp, size_t d) {
 	}
 	grp->acc_len = len;
 	grp->reduced = false;
-	return 0;
+	return stage_peer_table(grp, 0, grp->acc);
 }
 
 static int ensure_part(p1_group *grp, size_t len) {
@@ -326,7 +335,7 @@ static int ensure_part(p1_group *grp, size_t len) {
 		P1_CUDA(cudaMalloc(&grp->part[g], len * sizeof(uint64_t)));
 	}
 	grp->part_len = len;
-	return 0;
+	return stage_peer_table(grp, 1, grp->part);
 }
 
 extern "C" int p1_group_acc_reset(p1_group *grp, size_t d) {
@@ -478,9 +487,7 @@ extern "C" int p1_group_ti_generate_keys(p1_group *grp, const uint8_t key_x[16],
 	});
 	if(st || group_join(grp)) return 1;
 	if(xy_dev0 && grp->ndev > 1) {
-		std::vector<uint64_t *> bufs(grp->part);
-		bufs[0] = xy_dev0;
-		return reduce_p2p(grp, bufs, count);
+		return reduce_p2p(grp, 1, xy_dev0, count);
 	}
 	return 0;
 }

@@ -11,6 +11,8 @@ bookkeeping with numpy index arrays and torch device buffers (plumbing).
 import ctypes
 import math
 
+import time
+
 import numpy as np
 
 from . import ffi
@@ -449,10 +451,14 @@ class Phase1Box:
             t.cuda.current_stream(self.dev).synchronize()
         acc = self.acc.data_ptr()
         done = 0
+        self.ot_setup_s = 0.0           # host seconds of this call spent on session set-up and tear-down (bench.py reports it apart)
+        self.ot_sessions = 0
         self._fan_out()
         for ps, pr, items in self.ot_schedule():
             if max_pairs is not None and done >= max_pairs:
                 break
+            t_setup = time.perf_counter()
+            self.ot_sessions += 1
             seeds0, seeds1, delta = derive_cot_session(ot_key, ps + 2, pr + 2)
             chosen = np.ascontiguousarray(np.where(_bits128(delta)[:, None], seeds1, seeds0))
             sess = []
@@ -461,6 +467,7 @@ class Phase1Box:
                 L.check(L.p1_cot_sender_new(ctx, delta.tobytes(), ptr(chosen), ctypes.byref(snd)))
                 L.check(L.p1_cot_receiver_new(ctx, ptr(seeds0), ptr(seeds1), ctypes.byref(rcv)))
                 sess.append((snd, rcv))
+            self.ot_setup_s += time.perf_counter() - t_setup
             for k, (col_s, col_r, slot) in enumerate(items):
                 if max_pairs is not None and done >= max_pairs:
                     break
@@ -477,8 +484,11 @@ class Phase1Box:
                 done += 1
             for ctx, (snd, rcv) in zip(self.ctxs[:npipe], sess):
                 L.check(L.p1_ctx_sync(ctx))
+            t_setup = time.perf_counter()
+            for snd, rcv in sess:
                 L.p1_cot_free(snd)
                 L.p1_cot_free(rcv)
+            self.ot_setup_s += time.perf_counter() - t_setup
         self._fan_in()
         return done
 

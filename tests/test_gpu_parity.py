@@ -773,3 +773,21 @@ def test_row_shards_combine_exactly(p1lib, oracle):
     assert np.array_equal(got, want)
     for b in boxes:
         b.close()
+
+
+def test_pool_blocks_come_back_zeroed(p1lib):
+    """a block that p1_dev_free keeps for the next request of its size is zeroed first (include/p1gpu.h, P1GPU_POOL_SCRUB
+    default 1): what one owner kept in it - masks, keys, messages - is not handed to the next"""
+    ctx = mkctx(p1lib)
+    nbytes = 3 * 4096 + 16          # a size nothing else in the suite asks for
+    junk = np.full(nbytes, 0xA5, np.uint8)
+    p = dev_array(p1lib, ctx, junk)
+    assert to_host(p1lib, ctx, p, nbytes, np.uint8).all()
+    first = p.value
+    p1lib.check(p1lib.p1_dev_free(ctx, p))
+    q = c_vp()
+    p1lib.check(p1lib.p1_dev_alloc(ctx, nbytes, ctypes.byref(q)))
+    assert q.value == first, "the pool did not hand the kept block back"
+    assert not to_host(p1lib, ctx, q, nbytes, np.uint8).any()
+    p1lib.check(p1lib.p1_dev_free(ctx, q))
+    p1lib.p1_ctx_destroy(ctx)
