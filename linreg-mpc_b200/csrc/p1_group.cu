@@ -249,20 +249,50 @@ extern "C" int p1_group_create(const int *devices, int ndev, int ring_bits_p1, i
 	grp->ev.assign(ndev, NULL);
 	grp->acc.assign(ndev, NULL);
 	grp->part.assign(ndev, NULL);
-	for(int g = 0; g < ndev; g++) {
-		if(p1_ctx_create(devices[g], ring_bits_p1, ring_bits_p2, &grp->ctx[g])) { p1_group_destroy(grp); return 1; }
-		if(cudaEventCreateWithFlags(&grp->ev[g], cudaEventDisableTiming) != cudaSuccess) { p1_group_destroy(grp); return p1_fail("p1_group_create: cudaEventCreate failed"); }
+	// The first touch of a GPU in a process (primary context, loading this library's kernels onto it) takes the better
+	// part of a second, and enabling peer access costs time per ordered pair: one host thread per device does both,
+	// in two rounds (every context exists before any peer mapping is asked for), instead of one device after another.
+	{
+		std::vector<int> st(ndev, 0);
+		std::vector<std::thread> th;
+		for(int g = 0; g < ndev; g++) th.emplace_back([&, g] {
+			if(p1_ctx_create(devices[g], ring_bits_p1, ring_bits_p2, &grp->ctx[g])) { st[g] = 1; return; }
+			if(cudaEventCreateWithFlags(&grp->ev[g], cudaEventDisableTiming) != cudaSuccess) st[g] = 2;
+		});
+		for(auto &t : th) t.join();
+		for(int g = 0; g < ndev; g++) if(st[g]) {
+			p1_group_destroy(grp);
+			return st[g] == 1 ? 1 : p1_fail("p1_group_create: cudaEventCreate failed");
+		}
 	}
 	// peer access between every pair of distinct devices (NVLink / NVSwitch on the box)
-	for(int a = 0; a < ndev; a++) for(int b = 0; b < ndev; b++) {
-		if(devices[a] == devices[b]) continue;
-		int can = 0;
-		cudaDeviceCanAccessPeer(&can, devices[a], devices[b]);
-		if(!can) { p1_group_destroy(grp); return p1_fail("p1_group_create: device %d cannot access device %d (no P2P)", devices[a], devices[b]); }
-		cudaSetDevice(devices[a]);
-		cudaError_t e = cudaDeviceEnablePeerAccess(devices[b], 0);
-		if(e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { p1_group_destroy(grp); return p1_fail("cudaDeviceEnablePeerAccess(%d -> %d): %s", devices[a], devices[b], cudaGetErrorString(e)); }
-		cudaGetLastError();
+	{
+		std::vector<int> bad(ndev, -1);
+		std::vector<cudaError_t> err(ndev, cudaSuccess);
+		std::vector<std::thread> th;
+		for(int a = 0; a < ndev; a++) {
+			bool first = true;                     // a device listed twice (tests) is handled once
+			for(int k = 0; k < a; k++) if(devices[k] == devices[a]) first = false;
+			if(!first) continue;
+			th.emplace_back([&, a] {
+				cudaSetDevice(devices[a]);
+				for(int b = 0; b < ndev; b++) {
+					if(devices[a] == devices[b]) continue;
+					int can = 0;
+					cudaDeviceCanAccessPeer(&can, devices[a], devices[b]);
+					if(!can) { bad[a] = b; err[a] = cudaSuccess; return; }
+					cudaError_t e = cudaDeviceEnablePeerAccess(devices[b], 0);
+					cudaGetLastError();
+					if(e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { bad[a] = b; err[a] = e; return; }
+				}
+			});
+		}
+		for(auto &t : th) t.join();
+		for(int a = 0; a < ndev; a++) if(bad[a] >= 0) {
+			p1_group_destroy(grp);
+			if(err[a] == cudaSuccess) return p1_fail("p1_group_create: device %d cannot access device %d (no P2P)", devices[a], devices[bad[a]]);
+			return p1_fail("cudaDeviceEnablePeerAccess(%d -> %d): %s", devices[a], devices[bad[a]], cudaGetErrorString(err[a]));
+		}
 	}
 	cudaSetDevice(devices[0]);
 	if(cudaEventCreateWithFlags(&grp->ev_main, cudaEventDisableTiming) != cudaSuccess ||
