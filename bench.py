@@ -52,6 +52,37 @@ WORKLOADS = {
 }
 
 
+# index of BASELINE.json's config a workload instantiates (seed = 20170401 + cfg_index)
+CFG_INDEX = {"cfg2": 2, "cfg3": 3, "gram": 3, "cfg4": 4, "cfg4p5": 4, "cfg5": 5, "cfg5p20": 5, "tiny": 0}
+GEN_CHUNK = 4096          # rows per generator chunk (a multiple of the 256-row shard alignment)
+
+
+def synthetic_chunk(cfg_index, chunk, d):
+    """Rows [chunk * GEN_CHUNK, (chunk + 1) * GEN_CHUNK) of the instance of SURVEY.md 8d before the column scaling:
+    X ~ N(0,1) row-major, then the noise of those rows, from numpy.random.default_rng([20170401 + cfg_index, chunk]) -
+    one stream per row chunk, so that any row shard of any N generates exactly its rows of the SAME matrix in parallel
+    (a single sequential stream would make rank r draw everything before its rows)."""
+    rng = np.random.default_rng([20170401 + cfg_index, chunk])
+    return rng.standard_normal((GEN_CHUNK, d)), rng.standard_normal(GEN_CHUNK)
+
+
+def synthetic_rows(cfg_index, row0, n_rows, d, threads=8):
+    """(X, noise) of rows [row0, row0 + n_rows) as float64 arrays (unscaled); row0 must be a multiple of 256"""
+    from concurrent.futures import ThreadPoolExecutor
+    X = np.empty((n_rows, d))
+    e = np.empty(n_rows)
+    c0, c1 = row0 // GEN_CHUNK, (row0 + n_rows + GEN_CHUNK - 1) // GEN_CHUNK
+
+    def fill(c):
+        xc, ec = synthetic_chunk(cfg_index, c, d)
+        lo, hi = max(row0, c * GEN_CHUNK), min(row0 + n_rows, (c + 1) * GEN_CHUNK)
+        X[lo - row0:hi - row0] = xc[lo - c * GEN_CHUNK:hi - c * GEN_CHUNK]
+        e[lo - row0:hi - row0] = ec[lo - c * GEN_CHUNK:hi - c * GEN_CHUNK]
+    with ThreadPoolExecutor(max_workers=threads) as ex:      # numpy's generators release the GIL
+        list(ex.map(fill, range(c0, c1)))
+    return X, e
+
+
 def even_col_start(d, p):
     return [k * (d // p) for k in range(p)]  # experiments/generate_tests.py:54-61
 
@@ -72,6 +103,9 @@ PUBLISHED = {
 def workload_config(name, wl, aggregation):
     return {"workload": "%s: synthetic n=%d d=%d, %d providers (vertical split), %d-bit phase 1, %s, precision %d"
                         % (name, wl["n"], wl["d"], wl["p"], wl["bits_p1"], aggregation, wl["precision"]),
+            "data_seed": "numpy.random.default_rng([20170401 + %d, row chunk]) per 4096-row chunk (X row-major, then the chunk's noise), "
+                         "beta from default_rng(20170401 + %d): the same matrix for every N; deviation from SURVEY 8d's single stream: "
+                         "one stream per chunk so that shards generate in parallel" % (CFG_INDEX.get(name, 0), CFG_INDEX.get(name, 0)),
             "n": wl["n"], "d": wl["d"], "providers": wl["p"], "ring_bits": wl["bits_p1"], "aggregation": aggregation}
 
 
@@ -331,19 +365,25 @@ def main():
     per = shard_rows(n, world, 0)[1]
     assert n_rows > 0, "more ranks than 256-row blocks"
 
-    # synthetic instance per experiments/generate_tests.py:159-169 (X ~ N(0,1), columns scaled to
-    # max |.| = 1, beta ~ U(0,1), y = X beta + N(0, 0.1^2)), generated on the device per shard
-    g = torch.Generator(device=dev)
-    g.manual_seed(20170401 + 7919 * rank)
-    Xd = torch.randn((n_rows, d), dtype=torch.float64, device=dev, generator=g)
+    # synthetic instance per experiments/generate_tests.py:159-169 (X ~ N(0,1), columns scaled to max |.| = 1,
+    # beta ~ U(0,1), y = X beta + N(0, 0.1^2)) from the documented numpy seed, one stream per 4096-row chunk: every N and
+    # every rank sees its rows of the same matrix, and the CPU side can regenerate any of them (synthetic_rows)
+    cfg_index = CFG_INDEX[args.workload]
+    slab = 64 * GEN_CHUNK
+    Xd = torch.empty((n_rows, d), dtype=torch.float64, device=dev)
+    noise = torch.empty(n_rows, dtype=torch.float64, device=dev)
+    for r in range(0, n_rows, slab):
+        rows = min(slab, n_rows - r)
+        xs, es = synthetic_rows(cfg_index, row0 + r, rows, d, threads=max(1, min(16, (os.cpu_count() or 8) // max(1, min(world, 8)))))
+        Xd[r:r + rows] = torch.from_numpy(xs).to(dev)
+        noise[r:r + rows] = torch.from_numpy(es).to(dev)
     cmax = Xd.abs().amax(dim=0)
     if group is not None:
         dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
     Xd /= cmax
-    gb = torch.Generator(device=dev)
-    gb.manual_seed(20170401)
-    beta = torch.rand(d, dtype=torch.float64, device=dev, generator=gb)
-    yd = Xd @ beta + 0.1 * torch.randn(n_rows, dtype=torch.float64, device=dev, generator=g)
+    beta = torch.from_numpy(np.random.default_rng(20170401 + cfg_index).random(d)).to(dev)
+    yd = Xd @ beta + 0.1 * noise
+    del noise
     torch.cuda.synchronize()
 
     gram = {"auto": pkg.ffi.P1_GRAM_AUTO, "imad": pkg.ffi.P1_GRAM_IMAD, "tcgen05": pkg.ffi.P1_GRAM_TCGEN05}[args.gram]

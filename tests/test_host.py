@@ -222,3 +222,18 @@ def test_seeded_mask_messages_of_the_dropin():
         out = (ctypes.c_uint8 * 16)()
         L.p1host_selftest_party_key(key, party, out)
         assert bytes(out) == hashlib.sha256(b"linreg-mpc p1gpu seeded mask key" + key + party.to_bytes(4, "little")).digest()[:16]
+
+
+def test_bench_instance_is_the_same_matrix_for_every_row_shard():
+    """bench.py's synthetic instance comes from one numpy stream per 4096-row chunk: a rank that generates
+    only its shard gets exactly its rows of the matrix a single GPU generates, whatever N is"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    d, n = 7, 3 * b.GEN_CHUNK + 300
+    X, e = b.synthetic_rows(3, 0, n, d, threads=2)
+    for row0, rows in ((256, 5000), (b.GEN_CHUNK, b.GEN_CHUNK), (2 * b.GEN_CHUNK + 256, n - 2 * b.GEN_CHUNK - 256)):
+        Xs, es = b.synthetic_rows(3, row0, rows, d, threads=3)
+        assert np.array_equal(Xs, X[row0:row0 + rows]) and np.array_equal(es, e[row0:row0 + rows])
+    assert not np.array_equal(b.synthetic_rows(4, 0, 256, d)[0], X[:256])      # another config, another matrix
